@@ -1,0 +1,171 @@
+/* rbx.h -- C ABI of the B200 (sm_100a) sketching kernels behind the RandBLAS C++ surface.
+ *
+ * Every entry point is what a RandBLAS maintainer would bind in place of the body of one reference
+ * function (file:line under the RandBLAS tree is cited at each declaration; INTEGRATION.md shows the
+ * header-side stub). Plain pointers and sizes only; no C++ or torch types cross this boundary.
+ *
+ * Conventions
+ *   layout 'C' (ColMajor) / 'R' (RowMajor); op 'N' / 'T'; side 'L' / 'R';
+ *   family 'G' (Gaussian) / 'U' (uniform, scaled by sqrt(3) in fill_dense like dense_skops.hh:511-513);
+ *   major axis 'S' (Short) / 'L' (Long)  -- same characters as RandBLAS::MajorAxis;
+ *   RNG state = uint32 ctr[4] (128-bit little-endian counter) + uint32 key[2]  (base.hh:161-232);
+ *   `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *   Pointers named *_dev are device pointers; the rbx_host_* variants take host pointers and stage
+ *   through device memory (copies are part of the call).
+ *   Return value: RBX_OK or a negative RBX_ERR_* code; rbx_strerror() names it. No exceptions cross.
+ *   There is no CPU fallback: without a CUDA device every compute entry point returns RBX_ERR_NO_DEVICE.
+ */
+#ifndef RBX_H
+#define RBX_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RBX_OK              0
+#define RBX_ERR_ARG        -1   /* a precondition the reference checks with randblas_require failed */
+#define RBX_ERR_CUDA       -2   /* a CUDA runtime call or kernel launch failed */
+#define RBX_ERR_NO_DEVICE  -3   /* no sm_100 device visible */
+#define RBX_ERR_ALLOC      -4   /* device workspace allocation failed */
+#define RBX_ERR_UNSUPPORTED -5  /* valid in the reference, not implemented on the device yet */
+
+const char* rbx_strerror(int code);
+const char* rbx_version(void);
+int rbx_device_count(void);
+/* number of kernel launches issued by this library in this process so far (for bench accounting) */
+int64_t rbx_launch_count(void);
+
+/* ---- RNG state algebra (host-side, exact) ------------------------------------------------------ */
+/* ctr += n with carry: Random123 array.h incr(); pinned by test/test_basic_rng/test_r123.cc:679-766 */
+void rbx_ctr_add(uint32_t ctr[4], uint64_t n);
+/* dense::compute_next_state, dense_skops.hh:172-191 */
+void rbx_dense_next_state(int64_t n_rows, int64_t n_cols, char major_axis, const uint32_t ctr[4], uint32_t next_ctr[4]);
+/* sparse::compute_next_state, sparse_skops.hh:115-126 (reproduced as written there) */
+void rbx_sparse_next_state(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], uint32_t next_ctr[4]);
+/* dist_to_layout / major_axis_length, dense_skops.hh:297-316 */
+char rbx_dist_to_layout(int64_t n_rows, int64_t n_cols, char major_axis);
+int64_t rbx_major_axis_length(int64_t n_rows, int64_t n_cols, char major_axis);
+
+/* ---- raw generator (testing the device Philox / transforms against KATs) ------------------------ */
+/* out_dev[4*i..4*i+3] = Philox4x32-10(ctr + i, key), i < n.  r123_kat_vectors.txt:19-21 */
+int rbx_philox4x32_dev(const uint32_t ctr[4], const uint32_t key[2], int64_t n, uint32_t* out_dev, void* stream);
+/* r123ext::boxmul / uneg11 ::generate on (ctr + i, key): random_gen.hh:136-144,163-172 */
+int rbx_generate4_dev(char family, const uint32_t ctr[4], const uint32_t key[2], int64_t n, float* out_dev, void* stream);
+/* the float transforms on caller-chosen raw words (exhaustive sweeps against the host libm):
+ * (s,c)[i] = boxmuller(u0[i], u1[i]) */
+int rbx_boxmuller_raw_dev(int64_t n, const uint32_t* u0_dev, const uint32_t* u1_dev, float* s_dev, float* c_dev, void* stream);
+
+/* ---- dense operators ----------------------------------------------------------------------------- */
+/* dense::fill_dense_submat_impl<T,RNG,OP>, dense_skops.hh:96-170 */
+int rbx_fill_dense_submat_f32(char family, int64_t n_cols, float* smat_dev, int64_t n_srows, int64_t n_scols,
+                              int64_t ptr, const uint32_t ctr[4], const uint32_t key[2], int64_t lda,
+                              uint32_t next_ctr[4], void* stream);
+int rbx_fill_dense_submat_f64(char family, int64_t n_cols, double* smat_dev, int64_t n_srows, int64_t n_scols,
+                              int64_t ptr, const uint32_t ctr[4], const uint32_t key[2], int64_t lda,
+                              uint32_t next_ctr[4], void* stream);
+/* fill_dense(layout, D, n_rows, n_cols, ro_s, co_s, buff, seed), dense_skops.hh:486-532 */
+int rbx_fill_dense_f32(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis,
+                       int64_t n_rows, int64_t n_cols, int64_t ro_s, int64_t co_s, float* buff_dev,
+                       const uint32_t ctr[4], const uint32_t key[2], uint32_t next_ctr[4], void* stream);
+int rbx_fill_dense_f64(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis,
+                       int64_t n_rows, int64_t n_cols, int64_t ro_s, int64_t co_s, double* buff_dev,
+                       const uint32_t ctr[4], const uint32_t key[2], uint32_t next_ctr[4], void* stream);
+int rbx_host_fill_dense_f32(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis,
+                            int64_t n_rows, int64_t n_cols, int64_t ro_s, int64_t co_s, float* buff_host,
+                            const uint32_t ctr[4], const uint32_t key[2], uint32_t next_ctr[4]);
+int rbx_host_fill_dense_f64(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis,
+                            int64_t n_rows, int64_t n_cols, int64_t ro_s, int64_t co_s, double* buff_host,
+                            const uint32_t ctr[4], const uint32_t key[2], uint32_t next_ctr[4]);
+
+/* ---- sparse operators ---------------------------------------------------------------------------- */
+/* sparse::repeated_fisher_yates, sparse_skops.hh:53-113 (idxs_minor_dev / vals_dev may be NULL) */
+int rbx_repeated_fisher_yates_f32_i32(const uint32_t ctr[4], const uint32_t key[2], int64_t vec_nnz, int64_t dim_major,
+                                      int64_t dim_minor, int32_t* idxs_major_dev, int32_t* idxs_minor_dev, float* vals_dev, void* stream);
+int rbx_repeated_fisher_yates_f32_i64(const uint32_t ctr[4], const uint32_t key[2], int64_t vec_nnz, int64_t dim_major,
+                                      int64_t dim_minor, int64_t* idxs_major_dev, int64_t* idxs_minor_dev, float* vals_dev, void* stream);
+int rbx_repeated_fisher_yates_f64_i32(const uint32_t ctr[4], const uint32_t key[2], int64_t vec_nnz, int64_t dim_major,
+                                      int64_t dim_minor, int32_t* idxs_major_dev, int32_t* idxs_minor_dev, double* vals_dev, void* stream);
+int rbx_repeated_fisher_yates_f64_i64(const uint32_t ctr[4], const uint32_t key[2], int64_t vec_nnz, int64_t dim_major,
+                                      int64_t dim_minor, int64_t* idxs_major_dev, int64_t* idxs_minor_dev, double* vals_dev, void* stream);
+/* fill_sparse(SparseSkOp&), sparse_skops.hh:389-413: COO triplets rows/cols/vals of length
+ * vec_nnz * (long dim) for Short-axis (SASO) or vec_nnz * (short dim) for Long-axis (LASO) */
+int rbx_fill_sparse_f32_i32(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                            int32_t* rows_dev, int32_t* cols_dev, float* vals_dev, uint32_t next_ctr[4], void* stream);
+int rbx_fill_sparse_f32_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                            int64_t* rows_dev, int64_t* cols_dev, float* vals_dev, uint32_t next_ctr[4], void* stream);
+int rbx_fill_sparse_f64_i32(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                            int32_t* rows_dev, int32_t* cols_dev, double* vals_dev, uint32_t next_ctr[4], void* stream);
+int rbx_fill_sparse_f64_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                            int64_t* rows_dev, int64_t* cols_dev, double* vals_dev, uint32_t next_ctr[4], void* stream);
+int rbx_host_fill_sparse_f64_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                 int64_t* rows_host, int64_t* cols_host, double* vals_host, uint32_t next_ctr[4]);
+int rbx_host_fill_sparse_f32_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                 int64_t* rows_host, int64_t* cols_host, float* vals_host, uint32_t next_ctr[4]);
+
+/* ---- sketching with a dense operator: dense::lskge3 / dense::rskge3, skge.hh:173-215 / 320-364 ---- */
+/* side 'L': B(d x n) = alpha * op(submat(S)) * op(A) + beta * B, dims (p0,p1,p2) = (d, n, m)
+ * side 'R': B(m x d) = alpha * op(A) * op(submat(S)) + beta * B, dims (p0,p1,p2) = (m, d, n)
+ * submat(S) starts at (ro_s, co_s) of the D_rows x D_cols operator defined by (family, major_axis, ctr, key).
+ * S_buff_dev == NULL: the operator is generated inside the kernel and never written to memory.
+ * S_buff_dev != NULL: explicit operator (DenseSkOp::buff) stored in S_layout with the natural leading
+ * dimension (D_cols for 'R', D_rows for 'C'), as after fill_dense(DenseSkOp&), dense_skops.hh:583-592. */
+int rbx_sketch_dense_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                         int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                         const float* S_buff_dev, char S_layout, int64_t ro_s, int64_t co_s,
+                         const float* A_dev, int64_t lda, float beta, float* B_dev, int64_t ldb, void* stream);
+int rbx_sketch_dense_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                         int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                         const double* S_buff_dev, char S_layout, int64_t ro_s, int64_t co_s,
+                         const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
+int rbx_host_sketch_dense_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                              int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                              int64_t ro_s, int64_t co_s, const float* A_host, int64_t lda, float beta, float* B_host, int64_t ldb);
+int rbx_host_sketch_dense_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                              int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                              int64_t ro_s, int64_t co_s, const double* A_host, int64_t lda, double beta, double* B_host, int64_t ldb);
+
+/* ---- sketching with a sparse operator: sparse::lskges / sparse::rskges, skge.hh:485-510 / 616-641 -- */
+/* Implicit operator: the SASO/LASO defined by (S_rows, S_cols, vec_nnz, major_axis, ctr, key) is regenerated on
+ * the device (fill_sparse semantics, sparse_skops.hh:389-413); nothing proportional to nnz is returned. */
+int rbx_sketch_sparseop_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                            int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                            int64_t ro_s, int64_t co_s, const float* A_dev, int64_t lda, float beta, float* B_dev, int64_t ldb, void* stream);
+int rbx_sketch_sparseop_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                            int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                            int64_t ro_s, int64_t co_s, const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
+int rbx_host_sketch_sparseop_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                                 int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                 int64_t ro_s, int64_t co_s, const float* A_host, int64_t lda, float beta, float* B_host, int64_t ldb);
+int rbx_host_sketch_sparseop_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                                 int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                 int64_t ro_s, int64_t co_s, const double* A_host, int64_t lda, double beta, double* B_host, int64_t ldb);
+/* Explicit COO operator / COO sparse matrix times dense: left_spmm / right_spmm with a COOMatrix,
+ * spmm_dispatch.hh:48-200 + coo_spmm_impl.hh:79-162 (int64 indices, index_base Zero). */
+int rbx_spmm_coo_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                     int64_t S_rows, int64_t S_cols, int64_t nnz, const int64_t* rows_dev, const int64_t* cols_dev, const float* vals_dev,
+                     int64_t ro_s, int64_t co_s, const float* A_dev, int64_t lda, float beta, float* B_dev, int64_t ldb, void* stream);
+int rbx_spmm_coo_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                     int64_t S_rows, int64_t S_cols, int64_t nnz, const int64_t* rows_dev, const int64_t* cols_dev, const double* vals_dev,
+                     int64_t ro_s, int64_t co_s, const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
+
+/* ---- sketch_sparse: dense operator x sparse data, sparse_data::lsksp3 / rsksp3, sksp.hh:147-192 / 302-345 */
+/* fmt 'O' COO (idx0 = rows, idx1 = cols), 'R' CSR (idx0 = rowptr, idx1 = colidxs), 'C' CSC (idx0 = rowidxs,
+ * idx1 = colptr); int64 indices, index_base Zero. CSR/CSC require ro_a == co_a == 0 (spmm_dispatch.hh:99-104). */
+int rbx_sketch_sparsedata_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                              int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                              int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, int64_t nnz,
+                              const float* vals_dev, const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t ro_a, int64_t co_a,
+                              float beta, float* B_dev, int64_t ldb, void* stream);
+int rbx_sketch_sparsedata_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                              int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                              int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, int64_t nnz,
+                              const double* vals_dev, const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t ro_a, int64_t co_a,
+                              double beta, double* B_dev, int64_t ldb, void* stream);
+
+/* ---- sharding helper for the multi-GPU callers: rank's [start, start+len) of `total`, aligned ---- */
+void rbx_shard_range(int64_t total, int world, int rank, int64_t align, int64_t* start, int64_t* len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RBX_H */

@@ -1,0 +1,251 @@
+// C ABI (include/rbx.h): argument validation mirroring the reference's randblas_require checks, index
+// algebra that the reference does on the host (offset_and_ldim, dims_before_op, layout flips), and
+// dispatch to the sm_100a kernels. Nothing here computes sketches on the CPU.
+#include <atomic>
+#include <cmath>
+#include "rbx_kernels.cuh"
+
+namespace rbx {
+
+static std::atomic<int64_t> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static int require_device() {
+    static int cached = 0;   // 0 unknown, 1 ok, -1 none
+    if (cached == 0) {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess) { cudaGetLastError(); n = 0; }
+        int ok = -1;
+        if (n > 0) {
+            int dev = 0; cudaGetDevice(&dev);
+            cudaDeviceProp prop;
+            if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess && prop.major == 10) ok = 1;
+        }
+        cached = ok;
+    }
+    return cached == 1 ? RBX_OK : RBX_ERR_NO_DEVICE;
+}
+#define RBX_NEED_DEVICE() do { int rc__ = require_device(); if (rc__ != RBX_OK) return rc__; } while (0)
+#define RBX_REQUIRE(cond) do { if (!(cond)) return RBX_ERR_ARG; } while (0)
+#define RBX_TRY(expr) do { int rc__ = (expr); if (rc__ != RBX_OK) return rc__; } while (0)
+
+static inline bool is_layout(char c) { return c == 'C' || c == 'R'; }
+static inline bool is_op(char c) { return c == 'N' || c == 'T'; }
+
+// ---- dense fills ------------------------------------------------------------------------------------
+template <typename T>
+static int fill_dense_submat(char family, int64_t n_cols, T* smat, int64_t n_srows, int64_t n_scols, int64_t ptr,
+                             const uint32_t* ctr, const uint32_t* key, int64_t lda, uint32_t* next_ctr, void* stream) {
+    RBX_REQUIRE(family == 'G' || family == 'U');
+    if (lda <= 0) lda = n_scols; else RBX_REQUIRE(lda >= n_scols);          // dense_skops.hh:106-110
+    RBX_REQUIRE(n_cols >= n_scols && n_cols > 0 && ptr >= 0);               // dense_skops.hh:111
+    const int64_t r0 = ptr / n_cols, c0 = ptr % n_cols, W = (n_cols + 3) / 4;
+    if (next_ctr) {                                                          // dense_skops.hh:166-169
+        Ctr128 nx = ctr_add(ctr_add(mk_ctr(ctr), (uint64_t)(r0 * W + c0 / 4)), (uint64_t)(n_srows * W));
+        put_ctr(nx, next_ctr);
+    }
+    RBX_NEED_DEVICE();
+    return launch_fill_window<T>(family, n_cols, smat, n_srows, n_scols, r0, c0, mk_ctr(ctr), mk_key(key), lda, 1, false,
+                                 (cudaStream_t) stream);
+}
+
+template <typename T>
+static int fill_dense(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis, int64_t n_rows, int64_t n_cols,
+                      int64_t ro_s, int64_t co_s, T* buff, const uint32_t* ctr, const uint32_t* key, uint32_t* next_ctr, void* stream) {
+    RBX_REQUIRE(is_layout(layout));
+    RBX_REQUIRE(family == 'G' || family == 'U');                            // BlackBox / unknown: dense_skops.hh:515-520
+    RBX_REQUIRE(major_axis == 'L' || major_axis == 'S');
+    RBX_REQUIRE(n_rows >= 0 && n_cols >= 0 && ro_s >= 0 && co_s >= 0);
+    RBX_REQUIRE(D_rows >= n_rows + ro_s && D_cols >= n_cols + co_s);        // dense_skops.hh:488-489
+    const int64_t ma = major_axis_length(D_rows, D_cols, major_axis), W = (ma + 3) / 4;
+    const bool nat_row = natural_is_rowmajor(D_rows, D_cols, major_axis);
+    // natural RowMajor: parent = S; natural ColMajor: parent = S^T (dense_skops.hh:494-503)
+    const int64_t r0 = nat_row ? ro_s : co_s, c0 = nat_row ? co_s : ro_s;
+    const int64_t nsr = nat_row ? n_rows : n_cols, nsc = nat_row ? n_cols : n_rows;
+    if (next_ctr) {
+        Ctr128 nx = ctr_add(ctr_add(mk_ctr(ctr), (uint64_t)(r0 * W + c0 / 4)), (uint64_t)(nsr * W));
+        put_ctr(nx, next_ctr);
+    }
+    // strides of buff for (S row, S col), then for parent (row, col)
+    const int64_t s_r = (layout == 'C') ? 1 : n_cols, s_c = (layout == 'C') ? n_rows : 1;
+    const int64_t rs = nat_row ? s_r : s_c, cs = nat_row ? s_c : s_r;
+    RBX_NEED_DEVICE();
+    return launch_fill_window<T>(family, ma, buff, nsr, nsc, r0, c0, mk_ctr(ctr), mk_key(key), rs, cs, family == 'U',
+                                 (cudaStream_t) stream);
+}
+
+template <typename T>
+static int host_fill_dense(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis, int64_t n_rows, int64_t n_cols,
+                           int64_t ro_s, int64_t co_s, T* buff_host, const uint32_t* ctr, const uint32_t* key, uint32_t* next_ctr) {
+    RBX_NEED_DEVICE();
+    const size_t bytes = sizeof(T) * (size_t) n_rows * (size_t) n_cols;
+    T* dev = nullptr;
+    if (bytes == 0) return fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, dev, ctr, key, next_ctr, nullptr);
+    if (cudaMalloc(&dev, bytes) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    int rc = fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, dev, ctr, key, next_ctr, nullptr);
+    if (rc == RBX_OK && cudaMemcpy(buff_host, dev, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) rc = RBX_ERR_CUDA;
+    cudaFree(dev);
+    return rc;
+}
+
+// ---- sparse fills -----------------------------------------------------------------------------------
+template <typename T, typename I>
+static int fill_sparse(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t* ctr, const uint32_t* key,
+                       I* rows, I* cols, T* vals, uint32_t* next_ctr, void* stream) {
+    RBX_REQUIRE(major_axis == 'L' || major_axis == 'S');
+    RBX_REQUIRE(n_rows > 0 && n_cols > 0 && vec_nnz > 0);
+    const int64_t lng = n_rows > n_cols ? n_rows : n_cols, sht = n_rows < n_cols ? n_rows : n_cols;
+    const bool is_wide = (n_rows == sht);                                    // sparse_skops.hh:394
+    I* short_idx = is_wide ? rows : cols;
+    I* long_idx  = is_wide ? cols : rows;
+    if (next_ctr) rbx_sparse_next_state(n_rows, n_cols, vec_nnz, major_axis, ctr, next_ctr);
+    RBX_REQUIRE(vec_nnz <= (major_axis == 'S' ? sht : lng));                 // sparse_skops.hh:63
+    RBX_NEED_DEVICE();
+    if (major_axis == 'S')
+        return launch_fisher_yates<T, I>(mk_ctr(ctr), mk_key(key), vec_nnz, sht, lng, short_idx, long_idx, vals, (cudaStream_t) stream);
+    return launch_fisher_yates<T, I>(mk_ctr(ctr), mk_key(key), vec_nnz, lng, sht, long_idx, short_idx, vals, (cudaStream_t) stream);
+}
+
+template <typename T, typename I>
+static int host_fill_sparse(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t* ctr, const uint32_t* key,
+                            I* rows_h, I* cols_h, T* vals_h, uint32_t* next_ctr) {
+    RBX_NEED_DEVICE();
+    const int64_t lng = n_rows > n_cols ? n_rows : n_cols, sht = n_rows < n_cols ? n_rows : n_cols;
+    const size_t nnz = (size_t)(vec_nnz * (major_axis == 'S' ? lng : sht));
+    I *rows = nullptr, *cols = nullptr; T* vals = nullptr;
+    if (cudaMalloc(&rows, nnz * sizeof(I)) != cudaSuccess || cudaMalloc(&cols, nnz * sizeof(I)) != cudaSuccess ||
+        cudaMalloc(&vals, nnz * sizeof(T)) != cudaSuccess) {
+        cudaGetLastError(); cudaFree(rows); cudaFree(cols); cudaFree(vals);
+        return RBX_ERR_ALLOC;
+    }
+    int rc = fill_sparse<T, I>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, rows, cols, vals, next_ctr, nullptr);
+    if (rc == RBX_OK) {
+        if (cudaMemcpy(rows_h, rows, nnz * sizeof(I), cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(cols_h, cols, nnz * sizeof(I), cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(vals_h, vals, nnz * sizeof(T), cudaMemcpyDeviceToHost) != cudaSuccess) rc = RBX_ERR_CUDA;
+    }
+    cudaFree(rows); cudaFree(cols); cudaFree(vals);
+    return rc;
+}
+
+// ---- dense-operator sketches ------------------------------------------------------------------------
+// element strides (row, col) of a matrix stored in `layout` with leading dimension ld
+static inline void strides_of(char layout, int64_t ld, int64_t* s_row, int64_t* s_col) {
+    if (layout == 'C') { *s_row = 1; *s_col = ld; } else { *s_row = ld; *s_col = 1; }
+}
+
+template <typename T>
+static int dispatch_dense_gemm(const GemmOperands<T>& g, cudaStream_t stream);
+template <> int dispatch_dense_gemm<float>(const GemmOperands<float>& g, cudaStream_t stream) {
+    int rc = launch_sketch_dense_tc_f32(g, stream);
+    return rc == RBX_ERR_UNSUPPORTED ? launch_sketch_dense_simt<float>(g, stream) : rc;
+}
+template <> int dispatch_dense_gemm<double>(const GemmOperands<double>& g, cudaStream_t stream) {
+    int rc = launch_sketch_dense_tc_f64(g, stream);
+    return rc == RBX_ERR_UNSUPPORTED ? launch_sketch_dense_simt<double>(g, stream) : rc;
+}
+
+// Shared shape bookkeeping for both sides. The right sketch B = op(A) op(S) is run as B^T = op(S)^T op(A)^T.
+struct SketchShape {
+    int64_t M, N, K;            // output is M x N in "sketch-major" orientation: M = d always
+    int64_t rows_sub, cols_sub; // dims of submat(S) before op
+    bool s_trans;               // Sop[i, l] = S[ro + l, co + i] (true) or S[ro + i, co + l] (false)
+    int64_t sc_i, sc_j, sx_l, sx_j;
+};
+static int sketch_shape(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2,
+                        int64_t lda, int64_t ldb, bool check_lda, SketchShape* s) {
+    RBX_REQUIRE(side == 'L' || side == 'R');
+    RBX_REQUIRE(is_layout(layout) && is_op(opS) && is_op(opA));
+    RBX_REQUIRE(p0 >= 0 && p1 >= 0 && p2 >= 0);
+    int64_t a_r, a_c, b_r, b_c;
+    strides_of(layout, lda, &a_r, &a_c);
+    strides_of(layout, ldb, &b_r, &b_c);
+    if (side == 'L') {
+        const int64_t d = p0, n = p1, m = p2;
+        s->M = d; s->N = n; s->K = m;
+        s->rows_sub = (opS == 'N') ? d : m; s->cols_sub = (opS == 'N') ? m : d;
+        s->s_trans = (opS == 'T');
+        const int64_t rows_A = (opA == 'N') ? m : n, cols_A = (opA == 'N') ? n : m;
+        if (layout == 'C') { if (check_lda) RBX_REQUIRE(lda >= rows_A); RBX_REQUIRE(ldb >= d); }
+        else               { if (check_lda) RBX_REQUIRE(lda >= cols_A); RBX_REQUIRE(ldb >= n); }
+        s->sc_i = b_r; s->sc_j = b_c;                            // C[i, j] = B[i, j]
+        if (opA == 'N') { s->sx_l = a_r; s->sx_j = a_c; }        // X[l, j] = A[l, j]
+        else            { s->sx_l = a_c; s->sx_j = a_r; }        // X[l, j] = A[j, l]
+    } else {
+        const int64_t m = p0, d = p1, n = p2;
+        s->M = d; s->N = m; s->K = n;
+        s->rows_sub = (opS == 'N') ? n : d; s->cols_sub = (opS == 'N') ? d : n;
+        s->s_trans = (opS == 'N');                               // Sop[i, l] = op(S)[l, i]
+        const int64_t rows_A = (opA == 'N') ? m : n, cols_A = (opA == 'N') ? n : m;
+        if (layout == 'C') { if (check_lda) RBX_REQUIRE(lda >= rows_A); RBX_REQUIRE(ldb >= m); }
+        else               { if (check_lda) RBX_REQUIRE(lda >= cols_A); RBX_REQUIRE(ldb >= d); }
+        s->sc_i = b_c; s->sc_j = b_r;                            // C[i, j] = B[j, i]
+        if (opA == 'N') { s->sx_l = a_c; s->sx_j = a_r; }        // X[l, j] = A[j, l]
+        else            { s->sx_l = a_r; s->sx_j = a_c; }        // X[l, j] = A[l, j]
+    }
+    return RBX_OK;
+}
+
+template <typename T>
+static int sketch_dense(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                        int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t* ctr, const uint32_t* key,
+                        const T* S_buff, char S_layout, int64_t ro_s, int64_t co_s,
+                        const T* A, int64_t lda, T beta, T* B, int64_t ldb, void* stream) {
+    SketchShape s;
+    RBX_TRY(sketch_shape(side, layout, opS, opA, p0, p1, p2, lda, ldb, true, &s));
+    RBX_REQUIRE(ro_s >= 0 && co_s >= 0);
+    RBX_REQUIRE(D_rows >= s.rows_sub + ro_s && D_cols >= s.cols_sub + co_s);   // skge.hh:197-198 / dense_skops.hh:488-489
+    GemmOperands<T> g{};
+    g.C = B; g.sc_i = s.sc_i; g.sc_j = s.sc_j;
+    g.X = A; g.sx_l = s.sx_l; g.sx_j = s.sx_j;
+    g.M = s.M; g.N = s.N; g.K = s.K;
+    g.alpha = alpha; g.beta = beta;
+    if (S_buff) {
+        RBX_REQUIRE(is_layout(S_layout));
+        int64_t s_r, s_c;
+        strides_of(S_layout, S_layout == 'C' ? D_rows : D_cols, &s_r, &s_c);   // offset_and_ldim, base.hh:104-114
+        g.Sx = S_buff + ro_s * s_r + co_s * s_c;
+        g.ss_i = s.s_trans ? s_c : s_r;
+        g.ss_l = s.s_trans ? s_r : s_c;
+    } else {
+        RBX_TRY(make_dense_window(D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s, &g.w));
+        g.l_on_cols = ((!s.s_trans) == (g.w.parent_is_S != 0)) ? 1 : 0;
+        g.Sx = nullptr;
+    }
+    RBX_NEED_DEVICE();
+    return dispatch_dense_gemm<T>(g, (cudaStream_t) stream);
+}
+
+// number of elements spanned by a (rows x cols) matrix in `layout` with leading dimension ld
+static inline size_t span_elems(char layout, int64_t rows, int64_t cols, int64_t ld) {
+    if (rows <= 0 || cols <= 0) return 0;
+    return (layout == 'C') ? (size_t)((cols - 1) * ld + rows) : (size_t)((rows - 1) * ld + cols);
+}
+
+// Stage host A / B through device memory around `body(A_dev, B_dev, stream)`.
+template <typename T, typename F>
+static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_host, int64_t lda,
+                       int64_t rows_B, int64_t cols_B, T* B_host, int64_t ldb, bool read_B, F body) {
+    RBX_NEED_DEVICE();
+    const size_t nA = span_elems(layout, rows_A, cols_A, lda), nB = span_elems(layout, rows_B, cols_B, ldb);
+    T *A_dev = nullptr, *B_dev = nullptr;
+    cudaStream_t st = nullptr;
+    int rc = RBX_OK;
+    if ((nA && cudaMalloc(&A_dev, nA * sizeof(T)) != cudaSuccess) || (nB && cudaMalloc(&B_dev, nB * sizeof(T)) != cudaSuccess)) {
+        cudaGetLastError(); rc = RBX_ERR_ALLOC;
+    }
+    if (rc == RBX_OK && nA && cudaMemcpyAsync(A_dev, A_host, nA * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK && nB && read_B && cudaMemcpyAsync(B_dev, B_host, nB * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK) rc = body(A_dev, B_dev, (void*) st);
+    if (rc == RBX_OK && nB && cudaMemcpyAsync(B_host, B_dev, nB * sizeof(T), cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (cudaStreamSynchronize(st) != cudaSuccess && rc == RBX_OK) rc = RBX_ERR_CUDA;
+    cudaFree(A_dev); cudaFree(B_dev);
+    return rc;
+}
+
+static inline void host_dims(char side, char opA, int64_t p0, int64_t p1, int64_t p2,
+                             int64_t* rows_A, int64_t* cols_A, int64_t* rows_B, int64_t* cols_B) {
+    if (side == 'L') { const int64_t d = p0, n = p1, m = p2; *rows_A = (opA == 'N') ? m : n; *cols_A = (opA == 'N') ? n : m; *rows_B = d; *cols_B = n; }
+    else             { const int64_t m = p0, d = p1, n = p2; *rows_A = (opA == 'N') ? m : n; *cols_A = (opA == 'N') ? n : m; *rows_B = m; *cols_B = d; }
+}

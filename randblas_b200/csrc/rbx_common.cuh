@@ -1,0 +1,73 @@
+// Shared host/device helpers for the rbx kernels (error codes, launch checks, small index algebra).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "../../include/rbx.h"
+#include "rbx_rng.cuh"
+
+namespace rbx {
+
+constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+inline int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        std::fprintf(stderr, "[rbx] %s: %s\n", what, cudaGetErrorString(e));
+        return RBX_ERR_CUDA;
+    }
+    return RBX_OK;
+}
+#define RBX_CUDA_TRY(expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            std::fprintf(stderr, "[rbx] %s failed: %s\n", #expr, cudaGetErrorString(e__));   \
+            return RBX_ERR_CUDA;                                                             \
+        }                                                                                    \
+    } while (0)
+
+inline Ctr128 mk_ctr(const uint32_t* c) { Ctr128 r; for (int i = 0; i < 4; ++i) r.v[i] = c[i]; return r; }
+inline Key64  mk_key(const uint32_t* k) { Key64 r; r.v[0] = k[0]; r.v[1] = k[1]; return r; }
+inline void   put_ctr(const Ctr128& c, uint32_t* out) { if (out) for (int i = 0; i < 4; ++i) out[i] = c.v[i]; }
+
+// dist_to_layout / major_axis_length (dense_skops.hh:297-316)
+inline bool natural_is_rowmajor(int64_t n_rows, int64_t n_cols, char major_axis) {
+    const bool wide = n_rows < n_cols, lng = (major_axis == 'L');
+    return wide ? lng : !lng;
+}
+inline int64_t major_axis_length(int64_t n_rows, int64_t n_cols, char major_axis) {
+    const int64_t mx = n_rows > n_cols ? n_rows : n_cols, mn = n_rows < n_cols ? n_rows : n_cols;
+    return major_axis == 'L' ? mx : mn;
+}
+
+// A dense-distribution operator window as the kernels see it: entry (i, j) of op-free S[ro+i, co+j]
+// is lane ((pc0 + pj) & 3) of generate4(philox(ctr + (pr0 + pi) * W + (pc0 + pj) / 4)), where the
+// parent is S when the natural layout is RowMajor (pi = i, pj = j) and S^T otherwise (pi = j, pj = i).
+// dense_skops.hh:109-131,491-503.
+struct DenseOpWindow {
+    Ctr128 ctr; Key64 key;
+    int64_t W;          // counters per parent row = ceil(ma_len / 4)
+    int64_t pr0, pc0;   // window origin in parent coordinates
+    int parent_is_S;    // 1: parent rows are rows of S; 0: parent rows are columns of S
+    float scale;        // 1 for Gaussian, (float)sqrt(3) for uniform (applied in T precision by callers)
+    char family;
+};
+
+inline int make_dense_window(int64_t D_rows, int64_t D_cols, char family, char major_axis,
+                             const uint32_t* ctr, const uint32_t* key, int64_t ro_s, int64_t co_s,
+                             DenseOpWindow* w) {
+    if (family != 'G' && family != 'U') return RBX_ERR_ARG;
+    if (major_axis != 'L' && major_axis != 'S') return RBX_ERR_ARG;
+    const int64_t ma = major_axis_length(D_rows, D_cols, major_axis);
+    w->ctr = mk_ctr(ctr); w->key = mk_key(key);
+    w->W = (ma + 3) / 4;
+    w->parent_is_S = natural_is_rowmajor(D_rows, D_cols, major_axis) ? 1 : 0;
+    w->pr0 = w->parent_is_S ? ro_s : co_s;
+    w->pc0 = w->parent_is_S ? co_s : ro_s;
+    w->family = family;
+    w->scale = 1.0f;
+    return RBX_OK;
+}
+
+}  // namespace rbx

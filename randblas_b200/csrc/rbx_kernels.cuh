@@ -1,0 +1,67 @@
+// Internal launcher prototypes shared between the kernel translation units and the C ABI (rbx_capi.cu).
+#pragma once
+#include "rbx_common.cuh"
+
+namespace rbx {
+
+void count_launch();
+
+// ---- K1 -------------------------------------------------------------------------------------------
+template <typename T>
+int launch_fill_window(char family, int64_t n_cols_parent, T* out, int64_t n_srows, int64_t n_scols, int64_t r0, int64_t c0,
+                       const Ctr128& ctr, const Key64& key, int64_t rs, int64_t cs, bool do_scale, cudaStream_t stream);
+int launch_philox_stream(const Ctr128& ctr, const Key64& key, int64_t n, uint32_t* out, cudaStream_t stream);
+int launch_generate4_stream(char family, const Ctr128& ctr, const Key64& key, int64_t n, float* out, cudaStream_t stream);
+int launch_boxmuller_raw(int64_t n, const uint32_t* u0, const uint32_t* u1, float* s, float* c, cudaStream_t stream);
+
+// ---- K3 -------------------------------------------------------------------------------------------
+template <typename T, typename I>
+int launch_fisher_yates(const Ctr128& ctr, const Key64& key, int64_t vec_nnz, int64_t dim_major, int64_t dim_minor,
+                        I* idxs_major, I* idxs_minor, T* vals, cudaStream_t stream);
+
+// ---- K2 -------------------------------------------------------------------------------------------
+// C[i, j] = alpha * sum_l Sop[i, l] * X[l, j] + beta * C[i, j]
+template <typename T>
+struct GemmOperands {
+    T* C; int64_t sc_i, sc_j;              // M x N output, element strides
+    const T* X; int64_t sx_l, sx_j;        // K x N data, element strides
+    int64_t M, N, K;
+    T alpha, beta;
+    // implicit operator: Sop[i, l] = parent(pr0 + (l_on_cols ? i : l), pc0 + (l_on_cols ? l : i))
+    DenseOpWindow w; int l_on_cols;
+    // explicit operator (DenseSkOp::buff): Sop[i, l] = Sx[i * ss_i + l * ss_l]; nullptr => implicit
+    const T* Sx; int64_t ss_i, ss_l;
+    int64_t nbx;                           // column tiles (set by the launcher)
+};
+template <typename T> int launch_sketch_dense_simt(const GemmOperands<T>& g, cudaStream_t stream);
+// tensor-core paths; return RBX_ERR_UNSUPPORTED when the shape/layout is outside their envelope
+int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream);
+int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream);
+
+// ---- K4 / K5 --------------------------------------------------------------------------------------
+// C = beta * C over an M x N strided view (beta == 0 writes zeros without reading: util.hh:51-59)
+template <typename T> int launch_scale_view(T* C, int64_t M, int64_t N, int64_t sc_i, int64_t sc_j, T beta, cudaStream_t stream);
+
+// C[i, :] += alpha * v * X[l, :] for every COO entry (r, c, v) whose op'd coordinates fall in the window:
+// (i, l) = trans ? (c - co, r - ro) : (r - ro, c - co), 0 <= i < M, 0 <= l < K.
+template <typename T, typename I>
+int launch_coo_scatter(int64_t nnz, const I* rows, const I* cols, const T* vals, bool trans, int64_t ro, int64_t co,
+                       int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
+                       T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+
+// C[:, j] += alpha * v * Sd[:, l] for every sparse-data entry (p, q, v): (l, j) = trans ? (q - co, p - ro) : (p - ro, q - co);
+// Sd is the M x K operator window stored with i contiguous (Sd[i + l * M]).
+template <typename T>
+int launch_spdata_scatter(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
+                          int64_t M, int64_t N, int64_t K, T alpha, const T* Sd, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+
+// expand a CSR rowptr / CSC colptr (n_outer + 1 entries) into one outer index per nonzero
+int launch_expand_ptr(int64_t n_outer, const int64_t* ptr, int64_t* outer_idx, cudaStream_t stream);
+
+// fast SASO path (left sketch, wide Short-axis operator, contiguous rows of X); RBX_ERR_UNSUPPORTED otherwise
+template <typename T>
+int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_t S_cols, int64_t vec_nnz, int64_t ro, int64_t co,
+                     int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
+                     T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+
+}  // namespace rbx
