@@ -172,6 +172,15 @@ void orc_boxmuller_model(uint32_t u0, uint32_t u1, float* s_out, float* c_out) {
     *c_out = c * r;
 }
 
+/* boxmuller through the live host libm (model == 0) or the explicit-FMA models (model == 1) on arrays */
+void orc_boxmuller_arr(int64_t n, const uint32_t* u0, const uint32_t* u1, float* s, float* c, int model) {
+    #pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        if (model) orc_boxmuller_model(u0[i], u1[i], &s[i], &c[i]);
+        else orc_boxmuller(u0[i], u1[i], &s[i], &c[i]);
+    }
+}
+
 /* Compare the models with the live libm over u in [lo, hi) with the given stride.
  * Returns the number of inputs whose float bits differ; first_bad gets the first such u. */
 int64_t orc_sweep_sincos(uint64_t lo, uint64_t hi, uint64_t stride, uint32_t* first_bad) {

@@ -26,7 +26,11 @@ static int require_device() {
     }
     return cached == 1 ? RBX_OK : RBX_ERR_NO_DEVICE;
 }
-#define RBX_NEED_DEVICE() do { int rc__ = require_device(); if (rc__ != RBX_OK) return rc__; } while (0)
+// Every entry point validates its arguments BEFORE this macro, so a "dry run" stops here with the verdict of
+// the argument checks; the host-pointer wrappers use that to report RBX_ERR_ARG before touching the device.
+static thread_local bool t_dry_run = false;
+struct DryRun { DryRun() { t_dry_run = true; } ~DryRun() { t_dry_run = false; } };
+#define RBX_NEED_DEVICE() do { if (t_dry_run) return RBX_OK; int rc__ = require_device(); if (rc__ != RBX_OK) return rc__; } while (0)
 #define RBX_REQUIRE(cond) do { if (!(cond)) return RBX_ERR_ARG; } while (0)
 #define RBX_TRY(expr) do { int rc__ = (expr); if (rc__ != RBX_OK) return rc__; } while (0)
 
@@ -78,6 +82,7 @@ static int fill_dense(char layout, int64_t D_rows, int64_t D_cols, char family, 
 template <typename T>
 static int host_fill_dense(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis, int64_t n_rows, int64_t n_cols,
                            int64_t ro_s, int64_t co_s, T* buff_host, const uint32_t* ctr, const uint32_t* key, uint32_t* next_ctr) {
+    { DryRun dry; RBX_TRY(fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, (T*) nullptr, ctr, key, nullptr, nullptr)); }
     RBX_NEED_DEVICE();
     const size_t bytes = sizeof(T) * (size_t) n_rows * (size_t) n_cols;
     T* dev = nullptr;
@@ -110,6 +115,7 @@ static int fill_sparse(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char maj
 template <typename T, typename I>
 static int host_fill_sparse(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t* ctr, const uint32_t* key,
                             I* rows_h, I* cols_h, T* vals_h, uint32_t* next_ctr) {
+    { DryRun dry; RBX_TRY((fill_sparse<T, I>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, (I*) nullptr, (I*) nullptr, (T*) nullptr, nullptr, nullptr))); }
     RBX_NEED_DEVICE();
     const int64_t lng = n_rows > n_cols ? n_rows : n_cols, sht = n_rows < n_cols ? n_rows : n_cols;
     const size_t nnz = (size_t)(vec_nnz * (major_axis == 'S' ? lng : sht));
@@ -227,6 +233,7 @@ static inline size_t span_elems(char layout, int64_t rows, int64_t cols, int64_t
 template <typename T, typename F>
 static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_host, int64_t lda,
                        int64_t rows_B, int64_t cols_B, T* B_host, int64_t ldb, bool read_B, F body) {
+    { DryRun dry; RBX_TRY(body((const T*) nullptr, (T*) nullptr, nullptr)); }
     RBX_NEED_DEVICE();
     const size_t nA = span_elems(layout, rows_A, cols_A, lda), nB = span_elems(layout, rows_B, cols_B, ldb);
     T *A_dev = nullptr, *B_dev = nullptr;
@@ -249,3 +256,282 @@ static inline void host_dims(char side, char opA, int64_t p0, int64_t p1, int64_
     if (side == 'L') { const int64_t d = p0, n = p1, m = p2; *rows_A = (opA == 'N') ? m : n; *cols_A = (opA == 'N') ? n : m; *rows_B = d; *cols_B = n; }
     else             { const int64_t m = p0, d = p1, n = p2; *rows_A = (opA == 'N') ? m : n; *cols_A = (opA == 'N') ? n : m; *rows_B = m; *cols_B = d; }
 }
+
+// ---- sparse-operator sketches -----------------------------------------------------------------------
+template <typename T, typename I>
+static int spmm_coo(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                    int64_t S_rows, int64_t S_cols, int64_t nnz, const I* rows, const I* cols, const T* vals,
+                    int64_t ro_s, int64_t co_s, const T* A, int64_t lda, T beta, T* B, int64_t ldb, void* stream) {
+    SketchShape s;
+    RBX_TRY(sketch_shape(side, layout, opS, opA, p0, p1, p2, lda, ldb, true, &s));
+    RBX_REQUIRE(ro_s >= 0 && co_s >= 0 && nnz >= 0);
+    RBX_REQUIRE(S_rows >= s.rows_sub && S_cols >= s.cols_sub);               // spmm_dispatch.hh:94-96 (COO: >=)
+    RBX_NEED_DEVICE();
+    cudaStream_t st = (cudaStream_t) stream;
+    RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));    // spmm_dispatch.hh:122-132
+    if (alpha == (T) 0) return RBX_OK;                                       // spmm_dispatch.hh:134-135
+    return launch_coo_scatter<T, I>(nnz, rows, cols, vals, s.s_trans, ro_s, co_s, s.M, s.N, s.K, alpha,
+                                    A, s.sx_l, s.sx_j, B, s.sc_i, s.sc_j, st);
+}
+
+template <typename T>
+static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                           int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t* ctr, const uint32_t* key,
+                           int64_t ro_s, int64_t co_s, const T* A, int64_t lda, T beta, T* B, int64_t ldb, void* stream) {
+    SketchShape s;
+    RBX_TRY(sketch_shape(side, layout, opS, opA, p0, p1, p2, lda, ldb, true, &s));
+    RBX_REQUIRE(major_axis == 'L' || major_axis == 'S');
+    RBX_REQUIRE(S_rows > 0 && S_cols > 0 && vec_nnz > 0 && ro_s >= 0 && co_s >= 0);
+    RBX_REQUIRE(S_rows >= s.rows_sub && S_cols >= s.cols_sub);
+    const int64_t lng = S_rows > S_cols ? S_rows : S_cols, sht = S_rows < S_cols ? S_rows : S_cols;
+    RBX_REQUIRE(vec_nnz <= (major_axis == 'S' ? sht : lng));
+    RBX_NEED_DEVICE();
+    cudaStream_t st = (cudaStream_t) stream;
+    // streaming kernel for the SASO hot case; everything else regenerates the triplets and scatters
+    if (!s.s_trans && major_axis == 'S' && S_rows <= S_cols) {
+        int rc = launch_saso_fast<T>(mk_ctr(ctr), mk_key(key), S_rows, S_cols, vec_nnz, ro_s, co_s, s.M, s.N, s.K, alpha,
+                                     A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
+        if (rc != RBX_ERR_UNSUPPORTED) return rc;
+    }
+    RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));
+    if (alpha == (T) 0) return RBX_OK;
+    const size_t nnz = (size_t)(vec_nnz * (major_axis == 'S' ? lng : sht));
+    int64_t *rows = nullptr, *cols = nullptr; T* vals = nullptr;
+    if (cudaMallocAsync(&rows, nnz * 8, st) != cudaSuccess || cudaMallocAsync(&cols, nnz * 8, st) != cudaSuccess ||
+        cudaMallocAsync(&vals, nnz * sizeof(T), st) != cudaSuccess) {
+        cudaGetLastError();
+        if (rows) cudaFreeAsync(rows, st);
+        if (cols) cudaFreeAsync(cols, st);
+        return RBX_ERR_ALLOC;
+    }
+    int rc = fill_sparse<T, int64_t>(S_rows, S_cols, vec_nnz, major_axis, ctr, key, rows, cols, vals, nullptr, stream);
+    if (rc == RBX_OK)
+        rc = launch_coo_scatter<T, int64_t>((int64_t) nnz, rows, cols, vals, s.s_trans, ro_s, co_s, s.M, s.N, s.K, alpha,
+                                            A, s.sx_l, s.sx_j, B, s.sc_i, s.sc_j, st);
+    cudaFreeAsync(rows, st); cudaFreeAsync(cols, st); cudaFreeAsync(vals, st);
+    return rc;
+}
+
+// ---- dense operator x sparse data ---------------------------------------------------------------------
+template <typename T>
+static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                             int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t* ctr, const uint32_t* key,
+                             int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, int64_t nnz,
+                             const T* vals, const int64_t* idx0, const int64_t* idx1, int64_t ro_a, int64_t co_a,
+                             T beta, T* B, int64_t ldb, void* stream) {
+    SketchShape s;
+    RBX_TRY(sketch_shape(side, layout, opS, opA, p0, p1, p2, 0, ldb, false, &s));
+    RBX_REQUIRE(fmt == 'O' || fmt == 'R' || fmt == 'C');
+    RBX_REQUIRE(ro_s >= 0 && co_s >= 0 && ro_a >= 0 && co_a >= 0 && nnz >= 0);
+    RBX_REQUIRE(D_rows >= s.rows_sub + ro_s && D_cols >= s.cols_sub + co_s);     // sksp.hh:177-178
+    // op(submat(A)) is K x N (left: m x n) or N x K (right: m x n with m = N, n = K)
+    const int64_t a_m = (side == 'L') ? s.K : s.N, a_n = (side == 'L') ? s.N : s.K;
+    const int64_t rows_sub_A = (opA == 'N') ? a_m : a_n, cols_sub_A = (opA == 'N') ? a_n : a_m;
+    RBX_REQUIRE(A_rows >= rows_sub_A + ro_a && A_cols >= cols_sub_A + co_a);     // sksp.hh:175-176
+    if (fmt != 'O') {                                                            // spmm_dispatch.hh:97-104
+        RBX_REQUIRE(ro_a == 0 && co_a == 0);
+        RBX_REQUIRE(A_rows == rows_sub_A && A_cols == cols_sub_A);
+    }
+    DenseOpWindow w;
+    RBX_TRY(make_dense_window(D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s, &w));
+    const bool l_on_cols = ((!s.s_trans) == (w.parent_is_S != 0));
+    RBX_NEED_DEVICE();
+    cudaStream_t st = (cudaStream_t) stream;
+    RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));
+    if (alpha == (T) 0 || nnz == 0 || s.M == 0 || s.N == 0 || s.K == 0) return RBX_OK;
+
+    // per-nonzero (row, col) of the sparse matrix
+    const int64_t *prow = idx0, *pcol = idx1;
+    int64_t* expanded = nullptr;
+    if (fmt != 'O') {
+        if (cudaMallocAsync(&expanded, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+        int rc = (fmt == 'R') ? launch_expand_ptr(A_rows, idx0, expanded, st) : launch_expand_ptr(A_cols, idx1, expanded, st);
+        if (rc != RBX_OK) { cudaFreeAsync(expanded, st); return rc; }
+        if (fmt == 'R') { prow = expanded; pcol = idx1; } else { prow = idx0; pcol = expanded; }
+    }
+    // entry (p, q) of A sits at (l, j) of op(A) for the left sketch when opA == 'N'; the right sketch is
+    // transposed, so there (p, q) -> (j, l) when opA == 'N'.
+    const bool a_trans = (side == 'L') ? (opA == 'T') : (opA == 'N');
+    // the operator window is generated in slabs of the contraction axis, M x Ks at a time (i contiguous)
+    const int64_t budget = (int64_t) 4 << 30;
+    int64_t Ks = budget / ((int64_t) sizeof(T) * s.M);
+    if (Ks < 1) Ks = 1;
+    if (Ks > s.K) Ks = s.K;
+    T* Sd = nullptr;
+    if (cudaMallocAsync(&Sd, sizeof(T) * (size_t)(s.M * Ks), st) != cudaSuccess) {
+        cudaGetLastError();
+        if (expanded) cudaFreeAsync(expanded, st);
+        return RBX_ERR_ALLOC;
+    }
+    const int64_t ma = major_axis_length(D_rows, D_cols, major_axis);
+    int rc = RBX_OK;
+    for (int64_t l0 = 0; l0 < s.K && rc == RBX_OK; l0 += Ks) {
+        const int64_t kk = (s.K - l0 < Ks) ? s.K - l0 : Ks;
+        if (l_on_cols) rc = launch_fill_window<T>(family, ma, Sd, s.M, kk, w.pr0, w.pc0 + l0, w.ctr, w.key, 1, s.M, family == 'U', st);
+        else           rc = launch_fill_window<T>(family, ma, Sd, kk, s.M, w.pr0 + l0, w.pc0, w.ctr, w.key, s.M, 1, family == 'U', st);
+        if (rc != RBX_OK) break;
+        // shift the sparse offsets so that l is measured from the slab start
+        const int64_t ro = a_trans ? ro_a : ro_a + l0, co = a_trans ? co_a + l0 : co_a;
+        rc = launch_spdata_scatter<T>(nnz, prow, pcol, vals, a_trans, ro, co, s.M, s.N, kk, alpha, Sd, B, s.sc_i, s.sc_j, st);
+    }
+    cudaFreeAsync(Sd, st);
+    if (expanded) cudaFreeAsync(expanded, st);
+    return rc;
+}
+
+}  // namespace rbx
+
+// =====================================================================================================
+// extern "C" surface
+// =====================================================================================================
+using namespace rbx;
+
+extern "C" {
+
+const char* rbx_strerror(int code) {
+    switch (code) {
+        case RBX_OK: return "ok";
+        case RBX_ERR_ARG: return "argument check failed (the reference would throw RandBLAS::exceptions::Error)";
+        case RBX_ERR_CUDA: return "CUDA runtime or kernel launch failure";
+        case RBX_ERR_NO_DEVICE: return "no sm_100 CUDA device visible (there is no CPU fallback)";
+        case RBX_ERR_ALLOC: return "device workspace allocation failed";
+        case RBX_ERR_UNSUPPORTED: return "case not implemented on the device";
+        default: return "unknown rbx error code";
+    }
+}
+const char* rbx_version(void) { return "rbx 0.1 (sm_100a)"; }
+int rbx_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; } return n; }
+int64_t rbx_launch_count(void) { return g_launches.load(); }
+
+void rbx_ctr_add(uint32_t ctr[4], uint64_t n) { put_ctr(ctr_add(mk_ctr(ctr), n), ctr); }
+void rbx_dense_next_state(int64_t n_rows, int64_t n_cols, char major_axis, const uint32_t ctr[4], uint32_t next_ctr[4]) {
+    const int64_t major = major_axis_length(n_rows, n_cols, major_axis);
+    const int64_t minor = n_rows + (n_cols - major);
+    put_ctr(ctr_add(mk_ctr(ctr), (uint64_t)(((major + 3) / 4) * minor)), next_ctr);
+}
+void rbx_sparse_next_state(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], uint32_t next_ctr[4]) {
+    const int64_t lng = n_rows > n_cols ? n_rows : n_cols, sht = n_rows < n_cols ? n_rows : n_cols;
+    put_ctr(ctr_add(mk_ctr(ctr), (uint64_t)(vec_nnz * (major_axis == 'S' ? sht : lng))), next_ctr);
+}
+char rbx_dist_to_layout(int64_t n_rows, int64_t n_cols, char major_axis) { return natural_is_rowmajor(n_rows, n_cols, major_axis) ? 'R' : 'C'; }
+int64_t rbx_major_axis_length(int64_t n_rows, int64_t n_cols, char major_axis) { return major_axis_length(n_rows, n_cols, major_axis); }
+void rbx_shard_range(int64_t total, int world, int rank, int64_t align, int64_t* start, int64_t* len) {
+    if (align < 1) align = 1;
+    const int64_t units = (total + align - 1) / align;
+    const int64_t base = units / world, rem = units % world;
+    const int64_t u0 = rank * base + (rank < rem ? rank : rem), nu = base + (rank < rem ? 1 : 0);
+    int64_t s = u0 * align, e = (u0 + nu) * align;
+    if (s > total) s = total;
+    if (e > total) e = total;
+    *start = s; *len = e - s;
+}
+
+int rbx_philox4x32_dev(const uint32_t ctr[4], const uint32_t key[2], int64_t n, uint32_t* out_dev, void* stream) {
+    RBX_NEED_DEVICE();
+    return launch_philox_stream(mk_ctr(ctr), mk_key(key), n, out_dev, (cudaStream_t) stream);
+}
+int rbx_generate4_dev(char family, const uint32_t ctr[4], const uint32_t key[2], int64_t n, float* out_dev, void* stream) {
+    RBX_REQUIRE(family == 'G' || family == 'U');
+    RBX_NEED_DEVICE();
+    return launch_generate4_stream(family, mk_ctr(ctr), mk_key(key), n, out_dev, (cudaStream_t) stream);
+}
+int rbx_boxmuller_raw_dev(int64_t n, const uint32_t* u0_dev, const uint32_t* u1_dev, float* s_dev, float* c_dev, void* stream) {
+    RBX_NEED_DEVICE();
+    return launch_boxmuller_raw(n, u0_dev, u1_dev, s_dev, c_dev, (cudaStream_t) stream);
+}
+
+#define RBX_DEF_DENSE(SUF, T)                                                                                                     \
+int rbx_fill_dense_submat_##SUF(char family, int64_t n_cols, T* smat_dev, int64_t n_srows, int64_t n_scols, int64_t ptr,          \
+                                const uint32_t ctr[4], const uint32_t key[2], int64_t lda, uint32_t next_ctr[4], void* stream) {  \
+    return fill_dense_submat<T>(family, n_cols, smat_dev, n_srows, n_scols, ptr, ctr, key, lda, next_ctr, stream);                \
+}                                                                                                                                 \
+int rbx_fill_dense_##SUF(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis, int64_t n_rows,               \
+                         int64_t n_cols, int64_t ro_s, int64_t co_s, T* buff_dev, const uint32_t ctr[4], const uint32_t key[2],   \
+                         uint32_t next_ctr[4], void* stream) {                                                                    \
+    return fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, buff_dev, ctr, key, next_ctr, stream); \
+}                                                                                                                                 \
+int rbx_host_fill_dense_##SUF(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis, int64_t n_rows,          \
+                              int64_t n_cols, int64_t ro_s, int64_t co_s, T* buff_host, const uint32_t ctr[4],                    \
+                              const uint32_t key[2], uint32_t next_ctr[4]) {                                                      \
+    return host_fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, buff_host, ctr, key, next_ctr); \
+}                                                                                                                                 \
+int rbx_sketch_dense_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,               \
+                           int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4],                   \
+                           const uint32_t key[2], const T* S_buff_dev, char S_layout, int64_t ro_s, int64_t co_s,                 \
+                           const T* A_dev, int64_t lda, T beta, T* B_dev, int64_t ldb, void* stream) {                            \
+    return sketch_dense<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key,               \
+                           S_buff_dev, S_layout, ro_s, co_s, A_dev, lda, beta, B_dev, ldb, stream);                               \
+}                                                                                                                                 \
+int rbx_host_sketch_dense_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,          \
+                                int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4],              \
+                                const uint32_t key[2], int64_t ro_s, int64_t co_s, const T* A_host, int64_t lda, T beta,          \
+                                T* B_host, int64_t ldb) {                                                                         \
+    int64_t rA, cA, rB, cB;                                                                                                       \
+    host_dims(side, opA, p0, p1, p2, &rA, &cA, &rB, &cB);                                                                         \
+    return with_staged<T>(layout, rA, cA, A_host, lda, rB, cB, B_host, ldb, beta != (T) 0,                                        \
+        [&](const T* A_dev, T* B_dev, void* st) {                                                                                 \
+            return sketch_dense<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key,       \
+                                   nullptr, 'C', ro_s, co_s, A_dev, lda, beta, B_dev, ldb, st); });                               \
+}                                                                                                                                 \
+int rbx_sketch_sparseop_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,            \
+                              int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4],            \
+                              const uint32_t key[2], int64_t ro_s, int64_t co_s, const T* A_dev, int64_t lda, T beta,             \
+                              T* B_dev, int64_t ldb, void* stream) {                                                              \
+    return sketch_sparseop<T>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, vec_nnz, major_axis, ctr, key,           \
+                              ro_s, co_s, A_dev, lda, beta, B_dev, ldb, stream);                                                  \
+}                                                                                                                                 \
+int rbx_host_sketch_sparseop_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,       \
+                                   int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4],       \
+                                   const uint32_t key[2], int64_t ro_s, int64_t co_s, const T* A_host, int64_t lda, T beta,       \
+                                   T* B_host, int64_t ldb) {                                                                      \
+    int64_t rA, cA, rB, cB;                                                                                                       \
+    host_dims(side, opA, p0, p1, p2, &rA, &cA, &rB, &cB);                                                                         \
+    return with_staged<T>(layout, rA, cA, A_host, lda, rB, cB, B_host, ldb, beta != (T) 0,                                        \
+        [&](const T* A_dev, T* B_dev, void* st) {                                                                                 \
+            return sketch_sparseop<T>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, vec_nnz, major_axis, ctr, key,   \
+                                      ro_s, co_s, A_dev, lda, beta, B_dev, ldb, st); });                                          \
+}                                                                                                                                 \
+int rbx_spmm_coo_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha, int64_t S_rows,   \
+                       int64_t S_cols, int64_t nnz, const int64_t* rows_dev, const int64_t* cols_dev, const T* vals_dev,          \
+                       int64_t ro_s, int64_t co_s, const T* A_dev, int64_t lda, T beta, T* B_dev, int64_t ldb, void* stream) {    \
+    return spmm_coo<T, int64_t>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, nnz, rows_dev, cols_dev, vals_dev,     \
+                                ro_s, co_s, A_dev, lda, beta, B_dev, ldb, stream);                                                \
+}                                                                                                                                 \
+int rbx_sketch_sparsedata_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,          \
+                                int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4],              \
+                                const uint32_t key[2], int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols,      \
+                                int64_t nnz, const T* vals_dev, const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t ro_a,   \
+                                int64_t co_a, T beta, T* B_dev, int64_t ldb, void* stream) {                                      \
+    return sketch_sparsedata<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key,          \
+                                ro_s, co_s, fmt, A_rows, A_cols, nnz, vals_dev, idx0_dev, idx1_dev, ro_a, co_a, beta, B_dev, ldb, stream); \
+}
+RBX_DEF_DENSE(f32, float)
+RBX_DEF_DENSE(f64, double)
+
+#define RBX_DEF_SPARSE(SUF, T, I)                                                                                                 \
+int rbx_repeated_fisher_yates_##SUF(const uint32_t ctr[4], const uint32_t key[2], int64_t vec_nnz, int64_t dim_major,             \
+                                    int64_t dim_minor, I* idxs_major_dev, I* idxs_minor_dev, T* vals_dev, void* stream) {         \
+    RBX_REQUIRE(vec_nnz <= dim_major);                                                                                            \
+    RBX_NEED_DEVICE();                                                                                                            \
+    return launch_fisher_yates<T, I>(mk_ctr(ctr), mk_key(key), vec_nnz, dim_major, dim_minor, idxs_major_dev, idxs_minor_dev,     \
+                                     vals_dev, (cudaStream_t) stream);                                                            \
+}                                                                                                                                 \
+int rbx_fill_sparse_##SUF(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4],                \
+                          const uint32_t key[2], I* rows_dev, I* cols_dev, T* vals_dev, uint32_t next_ctr[4], void* stream) {     \
+    return fill_sparse<T, I>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, rows_dev, cols_dev, vals_dev, next_ctr, stream);      \
+}
+RBX_DEF_SPARSE(f32_i32, float, int32_t)
+RBX_DEF_SPARSE(f32_i64, float, int64_t)
+RBX_DEF_SPARSE(f64_i32, double, int32_t)
+RBX_DEF_SPARSE(f64_i64, double, int64_t)
+
+int rbx_host_fill_sparse_f64_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                 int64_t* rows_host, int64_t* cols_host, double* vals_host, uint32_t next_ctr[4]) {
+    return host_fill_sparse<double, int64_t>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, rows_host, cols_host, vals_host, next_ctr);
+}
+int rbx_host_fill_sparse_f32_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                 int64_t* rows_host, int64_t* cols_host, float* vals_host, uint32_t next_ctr[4]) {
+    return host_fill_sparse<float, int64_t>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, rows_host, cols_host, vals_host, next_ctr);
+}
+
+}  // extern "C"

@@ -1,0 +1,370 @@
+"""GPU parity tests for the sketching kernels (K2 dense, K4 sparse operator, K5 sparse data) through the host mirror
+of the RandBLAS API. Tolerance = the reference's own componentwise bound (test/test_matmul_cores/linop_common.hh:257-263):
+    |B_hat - B| <= |alpha| * K * 2*eps * (|S||A|) + |beta| * eps * |B0|
+with eps the unit roundoff of T. Cases mirror test_lskge3.cc / test_rskge3.cc / test_lskges.cc / test_rskges.cc /
+test_spmm_*.cc / test_sketch_vector.cc / test_sketch_symmetric.cc."""
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+TDT = {"f32": torch.float32, "f64": torch.float64}
+EPS = {"f32": 2.0 ** -23, "f64": 2.0 ** -52}
+
+
+def mat(layout, rows, cols, ld, data):
+    """(rows x cols) numpy view of a flat buffer in `layout` with leading dimension ld"""
+    if layout == "C":
+        return np.lib.stride_tricks.as_strided(data, (rows, cols), (data.itemsize, ld * data.itemsize))
+    return np.lib.stride_tricks.as_strided(data, (rows, cols), (ld * data.itemsize, data.itemsize))
+
+
+def span(layout, rows, cols, ld):
+    return ((cols - 1) * ld + rows) if layout == "C" else ((rows - 1) * ld + cols)
+
+
+def dense_S(dt, D_rows, D_cols, fam, ma, ctr, key, rows, cols, ro, co):
+    rc, out, _ = ol.fill_dense(dt, "R", D_rows, D_cols, fam, ma, rows, cols, ro, co, ctr, key)
+    assert rc == 0
+    return out.reshape(rows, cols).astype(np.float64)
+
+
+def check_bound(dt, got, B0, Sop, Aop, alpha, beta, side, what):
+    """got, B0: (rowsB x colsB) float64 arrays; Sop/Aop: explicit op(submat(S)), op(A) as float64"""
+    P = Sop @ Aop if side == "L" else Aop @ Sop
+    exact = alpha * P + (beta * B0 if beta != 0 else 0)
+    K = Sop.shape[1] if side == "L" else Sop.shape[0]
+    absP = np.abs(Sop) @ np.abs(Aop) if side == "L" else np.abs(Aop) @ np.abs(Sop)
+    bound = abs(alpha) * K * 2 * EPS[dt] * absP + abs(beta) * EPS[dt] * np.abs(B0) + 1e-300
+    ratio = float(np.max(np.abs(got - exact) / bound))
+    assert ratio <= 1.0, f"{what}: error/bound = {ratio}"
+    return ratio
+
+
+def run_dense_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, D_extra=(0, 0), off=(0, 0), fam="G", ma="L",
+                   lda_pad=0, ldb_pad=0, key=(3, 0), prefilled=False):
+    rng = np.random.default_rng(d * 131 + n * 17 + m)
+    npdt = np.float32 if dt == "f32" else np.float64
+    if side == "L":
+        rowsS, colsS = (d, m) if opS == "N" else (m, d)
+        rowsA, colsA = (m, n) if opA == "N" else (n, m)
+        rowsB, colsB = d, n
+        dims = (d, n, m)
+    else:
+        # B (m x d) = op(A) (m x n) op(S) (n x d)
+        rowsS, colsS = (n, d) if opS == "N" else (d, n)
+        rowsA, colsA = (m, n) if opA == "N" else (n, m)
+        rowsB, colsB = m, d
+        dims = (m, d, n)
+    Dr, Dc = rowsS + off[0] + D_extra[0], colsS + off[1] + D_extra[1]
+    lda = (rowsA if layout == "C" else colsA) + lda_pad
+    ldb = (rowsB if layout == "C" else colsB) + ldb_pad
+    A = rng.standard_normal(span(layout, rowsA, colsA, lda)).astype(npdt)
+    B0 = rng.standard_normal(span(layout, rowsB, colsB, ldb)).astype(npdt)
+    S = rb.DenseSkOp(rb.DenseDist(Dr, Dc, fam, ma), rb.RNGState(list(key)), dtype=TDT[dt])
+    if prefilled:
+        rb.fill_dense(S)
+    dA, dB = torch.from_numpy(A).to(cuda), torch.from_numpy(B0.copy()).to(cuda)
+    L, O = rb.Layout(layout), rb.Op
+    if side == "L":
+        rb.sketch_general(L, O(opS), O(opA), *dims, alpha, S, off[0], off[1], dA, lda, beta, dB, ldb)
+    else:
+        rb.sketch_general(L, O(opA), O(opS), *dims, alpha, dA, lda, S, off[0], off[1], beta, dB, ldb)
+    got_flat = dB.cpu().numpy()
+    Sx = dense_S(dt, Dr, Dc, fam, ma, [0, 0, 0, 0], list(key), rowsS, colsS, off[0], off[1])
+    if fam == "U" and dt == "f32":
+        pass   # oracle already scales in float
+    Sop = Sx if opS == "N" else Sx.T
+    Aop = mat(layout, rowsA, colsA, lda, A).astype(np.float64)
+    Aop = Aop if opA == "N" else Aop.T
+    got = mat(layout, rowsB, colsB, ldb, got_flat).astype(np.float64)
+    B0m = mat(layout, rowsB, colsB, ldb, B0).astype(np.float64)
+    ratio = check_bound(dt, got, B0m, Sop, Aop, alpha, beta, side, (dt, side, layout, opS, opA, dims))
+    # padding of B (ld > rows/cols) must be untouched
+    if ldb_pad:
+        mask = np.ones(len(B0), bool)
+        idx = mat(layout, rowsB, colsB, ldb, np.arange(len(B0)))
+        mask[idx.ravel()] = False
+        assert np.array_equal(got_flat[mask], B0[mask])
+    return ratio
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+@pytest.mark.parametrize("layout", ["C", "R"])
+@pytest.mark.parametrize("side", ["L", "R"])
+def test_sketch_general_dense_small(rb, cuda, dt, layout, side):
+    """test_lskge3.cc / test_rskge3.cc: sketch, lift, transposed S, submatrix of S (offsets (3,1) in 8x12), submatrix of A"""
+    for opS in "NT":
+        for opA in "NT":
+            run_dense_case(rb, cuda, dt, side, layout, opS, opA, 7, 5, 19, 1.0, 0.0)
+            run_dense_case(rb, cuda, dt, side, layout, opS, opA, 19, 4, 7, 1.0, 0.0)              # lift
+    run_dense_case(rb, cuda, dt, side, layout, "N", "N", 5, 6, 11, 1.0, 0.0, D_extra=(0, 0), off=(3, 1))
+    run_dense_case(rb, cuda, dt, side, layout, "T", "N", 5, 6, 11, 1.0, 0.0, D_extra=(2, 3), off=(3, 1))
+    run_dense_case(rb, cuda, dt, side, layout, "N", "N", 7, 5, 19, 1.0, 0.0, lda_pad=3, ldb_pad=2)  # submatrix of A via lda
+    run_dense_case(rb, cuda, dt, side, layout, "N", "T", 7, 5, 19, 5.5, -1.0, lda_pad=1)            # alpha / beta
+    run_dense_case(rb, cuda, dt, side, layout, "N", "N", 7, 5, 19, 0.0, 2.0)
+    for fam in "GU":
+        for ma in "LS":
+            run_dense_case(rb, cuda, dt, side, layout, "N", "N", 9, 3, 33, 1.0, 0.0, fam=fam, ma=ma, off=(1, 2))
+            run_dense_case(rb, cuda, dt, side, layout, "T", "N", 9, 3, 33, 1.0, 0.0, fam=fam, ma=ma, off=(2, 1))
+    run_dense_case(rb, cuda, dt, side, layout, "N", "N", 7, 5, 19, 1.0, 0.5, prefilled=True, off=(1, 1), D_extra=(1, 1))
+    run_dense_case(rb, cuda, dt, side, layout, "T", "N", 7, 5, 19, 1.0, 0.5, prefilled=True)
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_sketch_general_dense_medium_ragged(rb, cuda, dt):
+    """sizes that are not multiples of any tile, both sides, unaligned operator offsets"""
+    for (side, layout, opS, opA, d, n, m, off) in [("L", "C", "N", "N", 130, 70, 517, (0, 0)), ("L", "R", "N", "N", 65, 129, 300, (5, 3)),
+                                                  ("L", "C", "T", "T", 100, 33, 257, (2, 7)), ("R", "C", "N", "N", 90, 64, 400, (1, 1)),
+                                                  ("R", "R", "T", "N", 64, 128, 256, (0, 0)), ("L", "C", "N", "N", 1, 1, 1000, (0, 1))]:
+        run_dense_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, 1.0, 0.0, off=off, D_extra=(3, 5))
+
+
+def test_nan_in_B_is_overwritten_when_beta_is_zero(rb, cuda):
+    """util::safe_scal (util.hh:51-59) / BLAS convention: beta == 0 never reads B"""
+    S = rb.DenseSkOp(rb.DenseDist(4, 9), 1)
+    A = torch.ones(9 * 3, device=cuda)
+    B = torch.full((12,), float("nan"), device=cuda)
+    rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 4, 3, 9, 1.0, S, 0, 0, A, 9, 0.0, B, 4)
+    assert bool(torch.isfinite(B).all())
+    Ss = rb.SparseSkOp(rb.SparseDist(4, 9, 2), 1, dtype=torch.float32)
+    B = torch.full((12,), float("nan"), device=cuda)
+    rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 4, 3, 9, 1.0, Ss, 0, 0, A, 9, 0.0, B, 4)
+    assert bool(torch.isfinite(B).all())
+
+
+# ---------------------------------------------------------------------------------------------- sparse operators
+def sparse_S_dense(dt, r, c, k, ma, ctr, key):
+    rc, rows, cols, vals, _ = ol.fill_sparse("f64", "i64", r, c, k, ma, ctr, key)
+    assert rc == 0
+    S = np.zeros((r, c))
+    np.add.at(S, (rows, cols), vals)
+    return S
+
+
+def run_sparseop_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, k, ma, D_extra=(0, 0), off=(0, 0), key=42,
+                      lda_pad=0, filled=False):
+    rng = np.random.default_rng(d * 7 + n * 3 + m + k)
+    npdt = np.float32 if dt == "f32" else np.float64
+    if side == "L":
+        rowsS, colsS = (d, m) if opS == "N" else (m, d)
+        rowsA, colsA = (m, n) if opA == "N" else (n, m)
+        rowsB, colsB, dims = d, n, (d, n, m)
+    else:
+        rowsS, colsS = (n, d) if opS == "N" else (d, n)
+        rowsA, colsA = (m, n) if opA == "N" else (n, m)
+        rowsB, colsB, dims = m, d, (m, d, n)
+    Sr, Sc = rowsS + off[0] + D_extra[0], colsS + off[1] + D_extra[1]
+    lda = (rowsA if layout == "C" else colsA) + lda_pad
+    ldb = rowsB if layout == "C" else colsB
+    A = rng.standard_normal(span(layout, rowsA, colsA, lda)).astype(npdt)
+    B0 = rng.standard_normal(rowsB * colsB).astype(npdt)
+    S = rb.SparseSkOp(rb.SparseDist(Sr, Sc, k, ma), key, dtype=TDT[dt])
+    if filled:
+        rb.fill_sparse(S)
+    dA, dB = torch.from_numpy(A).to(cuda), torch.from_numpy(B0.copy()).to(cuda)
+    L, O = rb.Layout(layout), rb.Op
+    if side == "L":
+        rb.sketch_general(L, O(opS), O(opA), *dims, alpha, S, off[0], off[1], dA, lda, beta, dB, ldb)
+    else:
+        rb.sketch_general(L, O(opA), O(opS), *dims, alpha, dA, lda, S, off[0], off[1], beta, dB, ldb)
+    Sfull = sparse_S_dense(dt, Sr, Sc, k, ma, [0, 0, 0, 0], [key, 0])
+    Sx = Sfull[off[0]:off[0] + rowsS, off[1]:off[1] + colsS]
+    Sop = Sx if opS == "N" else Sx.T
+    Aop = mat(layout, rowsA, colsA, lda, A).astype(np.float64)
+    Aop = Aop if opA == "N" else Aop.T
+    got = mat(layout, rowsB, colsB, ldb, dB.cpu().numpy()).astype(np.float64)
+    B0m = mat(layout, rowsB, colsB, ldb, B0).astype(np.float64)
+    check_bound(dt, got, B0m, Sop, Aop, alpha, beta, side, ("sparse", dt, side, layout, opS, opA, dims, k, ma))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+@pytest.mark.parametrize("layout", ["C", "R"])
+def test_sketch_general_sparse_operator(rb, cuda, dt, layout):
+    """test_lskges.cc:174-589 / test_rskges.cc: SASO & LASO, keys {42,0,1}, vec_nnz {1,2,3,7,19}, 19x201 * 201x12 and lifts,
+    row/col subsets of S, transposes, submatrix of A, alpha/beta."""
+    for ma in "SL":
+        for key in (42, 0, 1):
+            for k in (1, 2, 3, 7, 19):
+                run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 19, 12, 201, 1.0, 0.0, k, ma, key=key)
+        for k in (1, 3, 7):
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 201, 12, 19, 1.0, 0.0, k, ma)          # lift (tall S)
+            run_sparseop_case(rb, cuda, dt, "R", layout, "N", "N", 19, 12, 201, 1.0, 0.0, k, ma)          # A (12x201) S (201x19)
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 12, 9, 150, 1.0, 0.0, k, ma, D_extra=(7, 51), off=(0, 0))
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 12, 9, 150, 1.0, 0.0, k, ma, D_extra=(3, 11), off=(4, 40))
+            run_sparseop_case(rb, cuda, dt, "L", layout, "T", "N", 19, 12, 201, 1.0, 0.0, k, ma)
+            run_sparseop_case(rb, cuda, dt, "R", layout, "T", "T", 19, 12, 201, 1.0, 0.0, k, ma, off=(1, 2), D_extra=(1, 1))
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "T", 19, 12, 201, 1.0, 0.0, k, ma, lda_pad=5)
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 19, 12, 201, 5.5, -1.0, k, ma)
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 19, 12, 201, 5.5, 0.0, k, ma, filled=True)
+            run_sparseop_case(rb, cuda, dt, "R", layout, "N", "N", 19, 12, 201, 1.0, 0.5, k, ma, filled=True, off=(2, 1), D_extra=(0, 3))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_saso_medium(rb, cuda, dt):
+    """a config-2-shaped case at 1/64 scale in each dimension class: d=256, m=16384, n=96, vec_nnz=8, both layouts, offsets"""
+    for layout in "CR":
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 256, 96, 16384, 1.0, 0.0, 8, "S", key=1997)
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 200, 100, 10001, 2.0, 1.0, 8, "S", key=1997, off=(5, 1234), D_extra=(51, 77))
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 2048, 64, 4096, 1.0, 0.0, 8, "S", key=7)
+
+
+# ---------------------------------------------------------------------------------------------- sparse data
+def random_sparse(rng, rows, cols, density, npdt):
+    M = rng.standard_normal((rows, cols)) * (rng.random((rows, cols)) < density)
+    return M.astype(npdt)
+
+
+def to_fmt(rb, cuda, M, fmt):
+    import scipy.sparse as sp
+    t = lambda a, dt=None: torch.from_numpy(np.ascontiguousarray(a if dt is None else a.astype(dt))).to(cuda)
+    if fmt == "O":
+        c = sp.coo_matrix(M)
+        return rb.COOMatrix(M.shape[0], M.shape[1], t(c.data), t(c.row, np.int64), t(c.col, np.int64))
+    if fmt == "R":
+        c = sp.csr_matrix(M)
+        return rb.CSRMatrix(M.shape[0], M.shape[1], t(c.data), t(c.indptr, np.int64), t(c.indices, np.int64))
+    c = sp.csc_matrix(M)
+    return rb.CSCMatrix(M.shape[0], M.shape[1], t(c.data), t(c.indices, np.int64), t(c.indptr, np.int64))
+
+
+def run_sparsedata_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, fmt, density, off_s=(0, 0), off_a=(0, 0), fam="G", ma="L"):
+    rng = np.random.default_rng(d + 3 * n + 7 * m + int(100 * density))
+    npdt = np.float32 if dt == "f32" else np.float64
+    if side == "L":
+        rowsS, colsS = (d, m) if opS == "N" else (m, d)
+        rowsA, colsA = (m, n) if opA == "N" else (n, m)
+        rowsB, colsB, dims = d, n, (d, n, m)
+    else:
+        rowsS, colsS = (n, d) if opS == "N" else (d, n)
+        rowsA, colsA = (m, n) if opA == "N" else (n, m)
+        rowsB, colsB, dims = m, d, (m, d, n)
+    Dr, Dc = rowsS + off_s[0] + 2, colsS + off_s[1] + 1
+    Ar, Ac = rowsA + off_a[0] + (3 if fmt == "O" and off_a != (0, 0) else 0), colsA + off_a[1]
+    Afull = random_sparse(rng, Ar, Ac, density, npdt)
+    Asp = to_fmt(rb, cuda, Afull, fmt)
+    ldb = rowsB if layout == "C" else colsB
+    B0 = rng.standard_normal(rowsB * colsB).astype(npdt)
+    dB = torch.from_numpy(B0.copy()).to(cuda)
+    S = rb.DenseSkOp(rb.DenseDist(Dr, Dc, fam, ma), 11, dtype=TDT[dt])
+    L, O = rb.Layout(layout), rb.Op
+    if side == "L":
+        rb.sketch_sparse(L, O(opS), O(opA), *dims, alpha, S, off_s[0], off_s[1], Asp, off_a[0], off_a[1], beta, dB, ldb)
+    else:
+        rb.sketch_sparse(L, O(opA), O(opS), *dims, alpha, Asp, off_a[0], off_a[1], S, off_s[0], off_s[1], beta, dB, ldb)
+    Sx = dense_S(dt, Dr, Dc, fam, ma, [0, 0, 0, 0], [11, 0], rowsS, colsS, off_s[0], off_s[1])
+    Sop = Sx if opS == "N" else Sx.T
+    Ax = Afull[off_a[0]:off_a[0] + rowsA, off_a[1]:off_a[1] + colsA].astype(np.float64)
+    Aop = Ax if opA == "N" else Ax.T
+    got = mat(layout, rowsB, colsB, ldb, dB.cpu().numpy()).astype(np.float64)
+    B0m = mat(layout, rowsB, colsB, ldb, B0).astype(np.float64)
+    check_bound(dt, got, B0m, Sop, Aop, alpha, beta, side, ("spdata", dt, side, layout, opS, opA, dims, fmt))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+@pytest.mark.parametrize("fmt", ["O", "R", "C"])
+def test_sketch_sparse(rb, cuda, dt, fmt):
+    """test_spmm_{coo,csr,csc}.cc through lsksp3/rsksp3: p in {0.01, 0.1, 0.8}, alpha/beta, transposes, submatrices
+    (of the sparse matrix: COO only, spmm_dispatch.hh:99-104)"""
+    for layout in "CR":
+        for side in "LR":
+            for density in (0.01, 0.1, 0.8):
+                run_sparsedata_case(rb, cuda, dt, side, layout, "N", "N", 7, 15, 40, 1.0, 0.0, fmt, density)
+            for opS in "NT":
+                for opA in "NT":
+                    run_sparsedata_case(rb, cuda, dt, side, layout, opS, opA, 6, 10, 25, 0.5, -1.5, fmt, 0.2, off_s=(1, 2))
+            if fmt == "O":
+                run_sparsedata_case(rb, cuda, dt, side, layout, "N", "N", 6, 10, 25, 1.0, 0.0, fmt, 0.3, off_a=(2, 3))
+                run_sparsedata_case(rb, cuda, dt, side, layout, "N", "T", 6, 10, 25, 1.0, 0.0, fmt, 0.3, off_a=(1, 4))
+            for fam in "GU":
+                for ma in "LS":
+                    run_sparsedata_case(rb, cuda, dt, side, layout, "N", "N", 9, 12, 31, 1.0, 0.0, fmt, 0.15, fam=fam, ma=ma, off_s=(2, 3))
+    if fmt != "O":
+        A = to_fmt(rb, cuda, random_sparse(np.random.default_rng(0), 20, 10, 0.3, np.float32 if dt == "f32" else np.float64), fmt)
+        S = rb.DenseSkOp(rb.DenseDist(5, 20), 0, dtype=TDT[dt])
+        B = torch.zeros(50, dtype=TDT[dt], device=cuda)
+        with pytest.raises(rb.Error):        # CSR/CSC: whole matrix only
+            rb.sketch_sparse(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 5, 9, 20, 1.0, S, 0, 0, A, 0, 1, 0.0, B, 5)
+
+
+# ---------------------------------------------------------------------------------------------- wrappers
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_sketch_vector(rb, cuda, dt):
+    """test_sketch_vector.cc: y = alpha op(S) x + beta y with strides"""
+    rng = np.random.default_rng(2)
+    npdt = np.float32 if dt == "f32" else np.float64
+    for (d, m, opS, incx, incy, off) in [(10, 30, "N", 1, 1, (0, 0)), (10, 30, "T", 2, 3, (0, 0)), (8, 25, "N", 3, 2, (2, 5)), (8, 25, "T", 1, 1, (1, 1))]:
+        for mk in ("dense", "sparse"):
+            Dr, Dc = d + off[0], m + off[1]
+            lx, ly = (m, d) if opS == "N" else (d, m)
+            x = rng.standard_normal(lx * incx).astype(npdt)
+            y0 = rng.standard_normal(ly * incy).astype(npdt)
+            if mk == "dense":
+                S = rb.DenseSkOp(rb.DenseDist(Dr, Dc), 5, dtype=TDT[dt])
+                Sfull = dense_S(dt, Dr, Dc, "G", "L", [0, 0, 0, 0], [5, 0], Dr, Dc, 0, 0)
+            else:
+                S = rb.SparseSkOp(rb.SparseDist(Dr, Dc, 3), 5, dtype=TDT[dt])
+                Sfull = sparse_S_dense(dt, Dr, Dc, 3, "S", [0, 0, 0, 0], [5, 0])
+            dx, dy = torch.from_numpy(x).to(cuda), torch.from_numpy(y0.copy()).to(cuda)
+            rb.sketch_vector(rb.Op(opS), d, m, 1.5, S, off[0], off[1], dx, incx, -0.5, dy, incy)
+            Sx = Sfull[off[0]:off[0] + d, off[1]:off[1] + m]
+            Sop = Sx if opS == "N" else Sx.T
+            got = dy.cpu().numpy()[::incy][:ly].astype(np.float64).reshape(-1, 1)
+            check_bound(dt, got, y0[::incy][:ly].astype(np.float64).reshape(-1, 1), Sop, x[::incx][:lx].astype(np.float64).reshape(-1, 1),
+                        1.5, -0.5, "L", ("vector", mk, opS))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_sketch_symmetric(rb, cuda, dt):
+    """test_sketch_symmetric.cc:89-155: both sides, both layouts, both major axes; asymmetric input is rejected"""
+    rng = np.random.default_rng(4)
+    npdt = np.float32 if dt == "f32" else np.float64
+    n, d = 23, 6
+    for layout in "CR":
+        for ma in "LS":
+            M = rng.standard_normal((n, n))
+            M = ((M + M.T) / 2).astype(npdt)
+            lda = n + 2
+            A = np.zeros(span(layout, n, n, lda), npdt)
+            mat(layout, n, n, lda, A)[:] = M
+            dA = torch.from_numpy(A).to(cuda)
+            # right: B (n x d) = A S,  S is n x d
+            S = rb.DenseSkOp(rb.DenseDist(n, d, "G", ma), 8, dtype=TDT[dt])
+            ldb = n if layout == "C" else d
+            dB = torch.zeros(n * d, dtype=TDT[dt], device=cuda)
+            rb.sketch_symmetric(rb.Layout(layout), n, d, 1.0, dA, lda, S, 0, 0, 0.0, dB, ldb)
+            Sx = dense_S(dt, n, d, "G", ma, [0, 0, 0, 0], [8, 0], n, d, 0, 0)
+            check_bound(dt, mat(layout, n, d, ldb, dB.cpu().numpy()).astype(np.float64), np.zeros((n, d)), Sx, M.astype(np.float64), 1.0, 0.0, "R", "symm-right")
+            # left: B (d x n) = S A,  S is d x n
+            S = rb.DenseSkOp(rb.DenseDist(d, n, "G", ma), 8, dtype=TDT[dt])
+            ldb = d if layout == "C" else n
+            dB = torch.zeros(n * d, dtype=TDT[dt], device=cuda)
+            rb.sketch_symmetric(rb.Layout(layout), d, n, 1.0, S, 0, 0, dA, lda, 0.0, dB, ldb)
+            Sx = dense_S(dt, d, n, "G", ma, [0, 0, 0, 0], [8, 0], d, n, 0, 0)
+            check_bound(dt, mat(layout, d, n, ldb, dB.cpu().numpy()).astype(np.float64), np.zeros((d, n)), Sx, M.astype(np.float64), 1.0, 0.0, "L", "symm-left")
+    bad = torch.from_numpy(rng.standard_normal(n * n).astype(npdt)).to(cuda)
+    with pytest.raises(rb.Error):
+        rb.sketch_symmetric(rb.Layout.ColMajor, n, d, 1.0, bad, n, rb.DenseSkOp(rb.DenseDist(n, d), 8, dtype=TDT[dt]), 0, 0, 0.0,
+                            torch.zeros(n * d, dtype=TDT[dt], device=cuda), n)
+
+
+def test_host_pointer_entry_points(rb, cuda):
+    """the rbx_host_* variants (host buffers, staged through HBM) give the same bits as the device-pointer calls"""
+    rng = np.random.default_rng(6)
+    A = torch.from_numpy(rng.standard_normal(300 * 20))
+    S = rb.SparseSkOp(rb.SparseDist(16, 300, 4), 3)
+    Bh = torch.zeros(16 * 20, dtype=torch.float64)
+    rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 16, 20, 300, 1.0, S, 0, 0, A, 300, 0.0, Bh, 16)
+    Bd = torch.zeros(16 * 20, dtype=torch.float64, device=cuda)
+    rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 16, 20, 300, 1.0, S, 0, 0, A.to(cuda), 300, 0.0, Bd, 16)
+    assert torch.allclose(Bh, Bd.cpu(), rtol=1e-13, atol=1e-13)
+    Sd = rb.DenseSkOp(rb.DenseDist(16, 300), 3, dtype=torch.float64)
+    rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 16, 20, 300, 1.0, Sd, 0, 0, A, 300, 0.0, Bh, 16)
+    rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 16, 20, 300, 1.0, Sd, 0, 0, A.to(cuda), 300, 0.0, Bd, 16)
+    assert torch.equal(Bh, Bd.cpu())
+    buf = torch.empty(16 * 300, dtype=torch.float32)
+    rb.fill_dense(rb.DenseDist(16, 300), buf, rb.RNGState(3))
+    rc, exp, _ = ol.fill_dense("f32", "R", 16, 300, "G", "L", 16, 300, 0, 0, [0, 0, 0, 0], [3, 0])
+    assert np.array_equal(buf.numpy().view(np.uint32), exp.view(np.uint32))
