@@ -8,6 +8,7 @@
 // lazily: only displaced positions are remembered, in a per-thread list of at most vec_nnz pairs.
 // Bit-exact by construction (integer arithmetic only).
 #include "rbx_kernels.cuh"
+#include "rbx_fy.cuh"
 
 namespace rbx {
 
@@ -18,29 +19,12 @@ __global__ void __launch_bounds__(128) fisher_yates_lazy_kernel(Ctr128 ctr, Key6
                                                                I* __restrict__ idxs_major, I* __restrict__ idxs_minor, T* __restrict__ vals) {
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= dim_minor) return;
-    int64_t pos[KMAX], val[KMAX];   // work[pos[t]] == val[t]; every other position still holds its own index
-    int nov = 0;
-    const bool small = dim_major <= 0xffffffffll;
-    for (int j = 0; j < vec_nnz; ++j) {
-        const uint4 rv = philox4x32_10(ctr_add(ctr, (uint64_t)(i * vec_nnz + j)), key);
-        const int64_t span = dim_major - j;
-        // ell = j + rv[0] % (dim_major - j)   (sparse_skops.hh:80-81; rv[0] promoted to int64)
-        const int64_t ell = j + (small ? (int64_t)(rv.x % (uint32_t) span) : (int64_t)((uint64_t) rv.x % (uint64_t) span));
-        int64_t at_ell = ell, at_j = j;
-        int slot = -1;
-        for (int t = 0; t < nov; ++t) {
-            if (pos[t] == ell) { at_ell = val[t]; slot = t; }
-            if (pos[t] == j) at_j = val[t];
-        }
-        if (ell != j) {                       // work[ell] <- work[j]; work[j] is never read again
-            if (slot < 0) { slot = nov++; pos[slot] = ell; }
-            val[slot] = at_j;
-        }
+    fy_vector<KMAX>(ctr, key, i, vec_nnz, dim_major, [&](int j, int64_t idx, bool negative) {
         const int64_t o = i * vec_nnz + j;
-        idxs_major[o] = (I) at_ell;
-        if (vals) vals[o] = (rv.y % 2 == 0) ? (T) 1.0 : (T) -1.0;
+        idxs_major[o] = (I) idx;
+        if (vals) vals[o] = negative ? (T) -1.0 : (T) 1.0;
         if (idxs_minor) idxs_minor[o] = (I) i;
-    }
+    });
 }
 
 // Fallback for vec_nnz > kLazyMax: one CTA walks vectors with an explicit work array in global scratch

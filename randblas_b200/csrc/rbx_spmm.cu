@@ -135,6 +135,34 @@ template int launch_spdata_scatter<float>(int64_t, const int64_t*, const int64_t
 template int launch_spdata_scatter<double>(int64_t, const int64_t*, const int64_t*, const double*, bool, int64_t, int64_t, int64_t, int64_t,
                                            int64_t, double, const double*, double*, int64_t, int64_t, cudaStream_t);
 
+// dst[l * ldd + j] = src[l + j * lds]  (K x N): column-major data re-laid with contiguous rows, 64x64 tiles through smem
+template <typename T>
+__global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ src, int64_t K, int64_t N, int64_t lds, T* __restrict__ dst, int64_t ldd) {
+    __shared__ T tile[64][65];
+    const int64_t l0 = (int64_t) blockIdx.x * 64, j0 = (int64_t) blockIdx.y * 64;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    for (int jj = ty; jj < 64; jj += 4) {
+        const int64_t l = l0 + tx, j = j0 + jj;
+        tile[jj][tx] = (l < K && j < N) ? __ldcs(src + l + j * lds) : (T) 0;
+    }
+    __syncthreads();
+    for (int ll = ty; ll < 64; ll += 4) {
+        const int64_t l = l0 + ll, j = j0 + tx;
+        if (l < K && j < N) dst[l * ldd + j] = tile[tx][ll];
+    }
+}
+template <typename T>
+int launch_transpose(const T* src, int64_t K, int64_t N, int64_t lds, T* dst, int64_t ldd, cudaStream_t stream) {
+    if (K <= 0 || N <= 0) return RBX_OK;
+    dim3 grid((unsigned)((K + 63) / 64), (unsigned)((N + 63) / 64));
+    if (grid.y > 65535u) return RBX_ERR_UNSUPPORTED;
+    transpose_kernel<T><<<grid, 256, 0, stream>>>(src, K, N, lds, dst, ldd);
+    count_launch();
+    return check_launch("transpose_kernel");
+}
+template int launch_transpose<float>(const float*, int64_t, int64_t, int64_t, float*, int64_t, cudaStream_t);
+template int launch_transpose<double>(const double*, int64_t, int64_t, int64_t, double*, int64_t, cudaStream_t);
+
 __global__ void __launch_bounds__(256) expand_ptr_kernel(int64_t n_outer, const int64_t* __restrict__ ptr, int64_t* __restrict__ outer_idx) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
