@@ -12,6 +12,7 @@
 //   * the operator is regenerated on the device (bit-exact Fisher-Yates, rbx_fy.cuh) by a small prep kernel that
 //     buckets each 128-column chunk of S by owning warp, in a deterministic order => run-to-run identical results.
 // Bound: HBM for float; for double the shared-memory gather (8 B per update, 128 B/clk/SM) is the tighter bound.
+#include <cstdlib>
 #include "rbx_kernels.cuh"
 #include "rbx_fy.cuh"
 #include "rbx_tma.cuh"
@@ -29,7 +30,7 @@ constexpr int SASO_THREADS = SASO_WARPS * 32;   // 512 threads => 128 registers 
 // ent[chunk * MC * k + off[chunk][b] ...] = 16-bit codes (c_local | r_local << 7 | negative << 12 | valid << 13), in (column, draw) order
 template <int KMAX>
 __global__ void __launch_bounds__(SASO_MC) saso_prep_kernel(Ctr128 ctr, Key64 key, int vec_nnz, int64_t dim_major, int64_t ro, int64_t co,
-                                                          int64_t M, int64_t K, int nbuckets, uint16_t* __restrict__ ent,
+                                                          int64_t M, int64_t K, int nbuckets, int off_stride, uint16_t* __restrict__ ent,
                                                           uint32_t* __restrict__ off) {
     extern __shared__ uint16_t sh[];
     uint16_t* code = sh;                               // MC * vec_nnz
@@ -58,7 +59,7 @@ __global__ void __launch_bounds__(SASO_MC) saso_prep_kernel(Ctr128 ctr, Key64 ke
     __syncthreads();
     if (t == 0) for (int b = 0; b < nbuckets; ++b) cnt[b + 1] += cnt[b];
     __syncthreads();
-    uint32_t* o = off + chunk * (nbuckets + 1);
+    uint32_t* o = off + chunk * off_stride;
     for (int b = t; b <= nbuckets; b += SASO_MC) o[b] = cnt[b];
     if (t < nbuckets) {
         uint16_t* dst = ent + chunk * total + cnt[t];
@@ -70,7 +71,7 @@ __global__ void __launch_bounds__(SASO_MC) saso_prep_kernel(Ctr128 ctr, Key64 ke
 template <typename T>
 struct SasoArgs {
     const uint16_t* ent; const uint32_t* off;
-    int vec_nnz, nbuckets, njb, msplit, nchunks;
+    int vec_nnz, nbuckets, njb, msplit, nchunks, nrb, dbg_skip;
     int64_t M, N;
     T alpha, beta;
     T* C; int64_t sc_i, sc_j;
@@ -124,115 +125,108 @@ __device__ __forceinline__ void acc_select16(float (&a)[16], uint32_t idx, float
         : "r"(idx), "f"(v));
 }
 
-template <typename T>
-__global__ void __launch_bounds__(SASO_THREADS, 1) saso_rows_kernel(const __grid_constant__ CUtensorMap tmap, const SasoArgs<T> a) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    T* stages = reinterpret_cast<T*>(smem);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t) SASO_NST * SASO_MC * SASO_W * sizeof(T));
-    uint64_t* empty = full + SASO_NST;
+// 16-byte asynchronous global->shared copy; bytes beyond src_bytes are zero-filled (ragged edges)
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-    const uint32_t cs = cluster_nctarank(), rank = cluster_ctarank();
+template <typename T>
+struct SasoStream {
+    const T* X; int64_t ldx; int64_t K, N;      // data: K x N, rows contiguous
+    int ent_stride;                             // codes per chunk (= MC * vec_nnz, a multiple of 8)
+    int off_stride;                             // uint32 per chunk row of `off` (multiple of 4)
+};
+
+template <typename T>
+__global__ void __launch_bounds__(SASO_THREADS, 1) saso_rows_kernel(const SasoStream<T> x, const SasoArgs<T> a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int A_BYTES = SASO_MC * SASO_W * (int) sizeof(T);
+    const int ent_bytes = x.ent_stride * 2, off_bytes = x.off_stride * 4;
+    const int stage_bytes = A_BYTES + ent_bytes + off_bytes;
+
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int cid = blockIdx.x / cs;
+    // the row blocks of one (column block, split) are adjacent block ids: they run together and share A through L2
+    const int rb = blockIdx.x % a.nrb;
+    const int cid = blockIdx.x / a.nrb;
     const int jb = cid % a.njb;
-    const int ms = (cid / a.njb) % a.msplit;
-    const int rg = cid / (a.njb * a.msplit);
+    const int ms = cid / a.njb;
     const int per = (a.nchunks + a.msplit - 1) / a.msplit;
     const int cb = ms * per;
     const int ce = (cb + per < a.nchunks) ? cb + per : a.nchunks;
+    const int64_t j0 = (int64_t) jb * SASO_W;
 
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < SASO_NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], cs * SASO_WARPS); }
-        fence_mbar_init();
-    }
-    cluster_sync_all();
-
-    // ===== producer duty (warp 0, lane 0): this CTA loads its 1/cs slice of every chunk into all CTAs of the cluster =====
-    const int rows_per = SASO_MC / (int) cs;
-    const uint16_t mask = (uint16_t)((1u << cs) - 1);
-    auto issue = [&](int it) {
-        const int s = it % SASO_NST;
-        mbar_expect_tx(&full[s], SASO_MC * SASO_W * sizeof(T));
-        T* dst = stages + (size_t) s * SASO_MC * SASO_W + (size_t) rank * rows_per * SASO_W;
-        const int y = (cb + it) * SASO_MC + (int) rank * rows_per;
-        if (cs > 1) tma_load_2d_mcast(dst, &tmap, jb * SASO_W, y, &full[s], mask);
-        else        tma_load_2d(dst, &tmap, jb * SASO_W, y, &full[s]);
+    auto load_stage = [&](int ch, int s) {
+        uint8_t* st = smem + (size_t) s * stage_bytes;
+        constexpr int PPR = SASO_W * (int) sizeof(T) / 16;          // 16-byte pieces per row
+        constexpr int EP = 16 / (int) sizeof(T);                    // elements per piece
+        for (int p = threadIdx.x; p < SASO_MC * PPR; p += SASO_THREADS) {
+            const int row = p / PPR, q = p % PPR;
+            const int64_t l = (int64_t) ch * SASO_MC + row, col = j0 + (int64_t) q * EP;
+            int64_t nb = (l < x.K) ? (x.N - col) * (int64_t) sizeof(T) : 0;
+            nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+            const T* src = nb > 0 ? x.X + l * x.ldx + col : x.X;
+            cp_async16(st + (size_t) p * 16, src, (uint32_t) nb);
+        }
+        const uint8_t* esrc = reinterpret_cast<const uint8_t*>(a.ent + (size_t) ch * x.ent_stride);
+        for (int p = threadIdx.x; p < ent_bytes / 16; p += SASO_THREADS) cp_async16(st + A_BYTES + p * 16, esrc + p * 16, 16);
+        const uint8_t* osrc = reinterpret_cast<const uint8_t*>(a.off + (size_t) ch * x.off_stride);
+        for (int p = threadIdx.x; p < off_bytes / 16; p += SASO_THREADS) cp_async16(st + A_BYTES + ent_bytes + p * 16, osrc + p * 16, 16);
     };
-    if (threadIdx.x == 0) {
-        tma_prefetch_desc(&tmap);
-        for (int it = 0; it < SASO_NST && cb + it < ce; ++it) issue(it);
+
+    // warp owns rows [bucket*32, bucket*32+32), lane owns column jb*32 + lane
+    const int bucket = rb * SASO_WARPS + warp;
+    const bool active = bucket < a.nbuckets;
+    T acc_lo[16], acc_hi[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { acc_lo[i] = (T) 0; acc_hi[i] = (T) 0; }
+
+    for (int s = 0; s < SASO_NST - 1; ++s) {
+        if (cb + s < ce) load_stage(cb + s, s);
+        cp_async_commit();
     }
-    __syncwarp();
-    {
-        // ===== consumers: warp owns rows [bucket*32, bucket*32+32), lane owns column jb*32 + lane =====
-        const int bucket = (rg * (int) cs + (int) rank) * SASO_WARPS + warp;
-        const bool active = bucket < a.nbuckets;
-        T acc_lo[16], acc_hi[16];
+    for (int ch = cb, it = 0; ch < ce; ++ch, ++it) {
+        cp_async_wait<SASO_NST - 2>();
+        __syncthreads();                                   // chunk `it` has landed; everyone is done with chunk it-1
+        if (ch + SASO_NST - 1 < ce) load_stage(ch + SASO_NST - 1, (it + SASO_NST - 1) % SASO_NST);
+        cp_async_commit();
+        if (!active || a.dbg_skip == 1) continue;
+        const uint8_t* st8 = smem + (size_t)(it % SASO_NST) * stage_bytes;
+        const T* st = reinterpret_cast<const T*>(st8) + lane;
+        const uint16_t* ents = reinterpret_cast<const uint16_t*>(st8 + A_BYTES);
+        const uint32_t* offs = reinterpret_cast<const uint32_t*>(st8 + A_BYTES + ent_bytes);
+        const uint32_t o0 = offs[bucket], o1 = offs[bucket + 1];
+        // four gathers in flight per step; slots beyond o1 are neutralised (valid bit clear => +0.0 into row 0)
+        for (uint32_t i = o0; i < o1; i += 4) {
+            uint32_t e[4]; T v[4];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { acc_lo[i] = (T) 0; acc_hi[i] = (T) 0; }
-        const int per_chunk = SASO_MC * a.vec_nnz;
-        uint32_t o0 = 0, o1 = 0, e_lane = 0;
-        if (active && cb < ce) {
-            const uint32_t* o = a.off + (size_t) cb * (a.nbuckets + 1) + bucket;
-            o0 = o[0]; o1 = o[1];
-            if (o0 + lane < o1) e_lane = a.ent[(size_t) cb * per_chunk + o0 + lane];
+            for (int q = 0; q < 4; ++q) { e[q] = (i + q < o1) ? ents[i + q] : 0u; v[q] = st[(e[q] & 127u) * SASO_W]; }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const T w = (e[q] & 0x2000u) ? flip_sign<T>(v[q], (e[q] >> 12) & 1u) : (T) 0;
+                if (a.dbg_skip == 2) acc_lo[0] += w; else
+                if (e[q] & 0x800u) acc_select16(acc_hi, (e[q] >> 7) & 15u, w); else acc_select16(acc_lo, (e[q] >> 7) & 15u, w);
+            }
         }
-        for (int ch = cb, it = 0; ch < ce; ++ch, ++it) {
-            const int s = it % SASO_NST;
-            const uint32_t ph = (it / SASO_NST) & 1;
-            // prefetch the next chunk's first 32 codes while this one is processed
-            uint32_t n0 = 0, n1 = 0, ne = 0;
-            if (active && ch + 1 < ce) {
-                const uint32_t* o = a.off + (size_t)(ch + 1) * (a.nbuckets + 1) + bucket;
-                n0 = o[0]; n1 = o[1];
-                if (n0 + lane < n1) ne = a.ent[(size_t)(ch + 1) * per_chunk + n0 + lane];
-            }
-            mbar_wait(&full[s], ph);
-            const T* st = stages + (size_t) s * SASO_MC * SASO_W + lane;
-            for (uint32_t base = o0; base < o1; base += 32) {
-                if (base != o0) e_lane = (base + lane < o1) ? a.ent[(size_t) ch * per_chunk + base + lane] : 0;
-                const int cnt = (o1 - base < 32u) ? (int)(o1 - base) : 32;
-                // four gathers in flight per step; codes beyond cnt are 0 (valid bit clear) and add +0.0 to row 0
-                for (int i = 0; i < cnt; i += 4) {
-                    uint32_t e[4]; T v[4];
+    }
+    cp_async_wait<0>();
+    if (active) {
+        const int64_t col = j0 + lane;
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) e[q] = __shfl_sync(0xffffffffu, e_lane, (i + q) & 31);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) { if (i + q >= cnt) e[q] = 0; v[q] = st[(e[q] & 127u) * SASO_W]; }
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const T w = (e[q] & 0x2000u) ? flip_sign<T>(v[q], (e[q] >> 12) & 1u) : (T) 0;
-                        if (e[q] & 0x800u) acc_select16(acc_hi, (e[q] >> 7) & 15u, w); else acc_select16(acc_lo, (e[q] >> 7) & 15u, w);
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane < (int) cs) mbar_arrive_cluster(&empty[s], lane);   // release the stage in every CTA that multicasts into it
-            if (threadIdx.x == 0 && ch + SASO_NST < ce) {               // refill it once every consumer of the cluster is done
-                mbar_wait_cluster(&empty[s], ph);
-                issue(it + SASO_NST);
-            }
-            __syncwarp();
-            o0 = n0; o1 = n1; e_lane = ne;
-        }
-        if (active) {
-            const int64_t col = (int64_t) jb * SASO_W + lane;
-#pragma unroll
-            for (int i = 0; i < SASO_RW; ++i) {
-                const T acc_i = i < 16 ? acc_lo[i & 15] : acc_hi[i & 15];
-                const int64_t row = (int64_t) bucket * SASO_RW + i;
-                if (row < a.M && col < a.N) {
-                    if (a.msplit == 1) {
-                        T* c = a.C + row * a.sc_i + col * a.sc_j;
-                        *c = (a.beta == (T) 0) ? a.alpha * acc_i : a.alpha * acc_i + a.beta * (*c);
-                    } else {
-                        a.partial[((size_t) ms * a.M + row) * ((size_t) a.njb * SASO_W) + col] = acc_i;
-                    }
+        for (int i = 0; i < SASO_RW; ++i) {
+            const T acc_i = i < 16 ? acc_lo[i & 15] : acc_hi[i & 15];
+            const int64_t row = (int64_t) bucket * SASO_RW + i;
+            if (row < a.M && col < a.N) {
+                if (a.msplit == 1) {
+                    T* c = a.C + row * a.sc_i + col * a.sc_j;
+                    *c = (a.beta == (T) 0) ? a.alpha * acc_i : a.alpha * acc_i + a.beta * (*c);
+                } else {
+                    a.partial[((size_t) ms * a.M + row) * ((size_t) a.njb * SASO_W) + col] = acc_i;
                 }
             }
         }
     }
-    cluster_sync_all();   // no CTA may exit while a sibling can still multicast into it or arrive on its barriers
 }
 
 template <typename T>
@@ -248,10 +242,6 @@ __global__ void __launch_bounds__(256) saso_reduce_kernel(const T* __restrict__ 
     }
 }
 
-template <typename T> struct TmapType;
-template <> struct TmapType<float>  { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_FLOAT32; };
-template <> struct TmapType<double> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_FLOAT64; };
-
 template <typename T>
 int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_t S_cols, int64_t vec_nnz, int64_t ro, int64_t co,
                      int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
@@ -265,19 +255,19 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
 
     const int nbuckets = (int)((M + SASO_RW - 1) / SASO_RW);
     const int nrb = (nbuckets + SASO_WARPS - 1) / SASO_WARPS;           // row blocks of 512 rows
-    int cs = 1; while (cs < nrb && cs < 8) cs *= 2;                     // cluster = row blocks sharing the A stream
-    const int nrg = (nrb + cs - 1) / cs;
     const int njb = (int)((N + SASO_W - 1) / SASO_W);
     const int nchunks = (int)((K + SASO_MC - 1) / SASO_MC);
-    // split the contraction axis so that the grid is several waves of co-resident clusters
-    const int conc = kNumSMs / cs;
-    int msplit = (4 * conc + njb * nrg - 1) / (njb * nrg);
+    // split the contraction axis so that the grid is several waves of CTAs (one CTA per SM)
+    int msplit = (6 * kNumSMs + njb * nrb - 1) / (njb * nrb);
     if (msplit > nchunks / 16) msplit = nchunks / 16;
     if (msplit < 1) msplit = 1;
+    if (const char* ev = getenv("RBX_SASO_MSPLIT")) { const int v = atoi(ev); if (v >= 1 && v <= nchunks) msplit = v; }
 
+    const int ent_stride = SASO_MC * (int) vec_nnz;                     // multiple of 128 codes => 16-byte multiple
+    const int off_stride = (nbuckets + 1 + 3) & ~3;
     uint16_t* ent = nullptr; uint32_t* off = nullptr; T* partial = nullptr;
-    const size_t ent_bytes = (size_t) nchunks * SASO_MC * vec_nnz * sizeof(uint16_t);
-    const size_t off_bytes = (size_t) nchunks * (nbuckets + 1) * sizeof(uint32_t);
+    const size_t ent_bytes = (size_t) nchunks * ent_stride * sizeof(uint16_t);
+    const size_t off_bytes = (size_t) nchunks * off_stride * sizeof(uint32_t);
     const size_t Np = (size_t) njb * SASO_W;
     const size_t part_bytes = msplit > 1 ? (size_t) msplit * M * Np * sizeof(T) : 0;
     if (cudaMallocAsync(&ent, ent_bytes, stream) != cudaSuccess || cudaMallocAsync(&off, off_bytes, stream) != cudaSuccess ||
@@ -290,37 +280,26 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     int rc = RBX_OK;
     {
         const size_t sh = (size_t) SASO_MC * vec_nnz * 2 * sizeof(uint16_t);
-        if (vec_nnz <= 8) saso_prep_kernel<8><<<nchunks, SASO_MC, sh, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, nbuckets, ent, off);
-        else              saso_prep_kernel<32><<<nchunks, SASO_MC, sh, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, nbuckets, ent, off);
+        if (vec_nnz <= 8) saso_prep_kernel<8><<<nchunks, SASO_MC, sh, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, nbuckets, off_stride, ent, off);
+        else              saso_prep_kernel<32><<<nchunks, SASO_MC, sh, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, nbuckets, off_stride, ent, off);
         count_launch();
         rc = check_launch("saso_prep_kernel");
     }
-    CUtensorMap tmap;
-    if (rc == RBX_OK && !make_tmap_2d(&tmap, TmapType<T>::v, X, (uint64_t) N, (uint64_t) K, (uint64_t) sx_l * sizeof(T), SASO_W, SASO_MC / cs))
-        rc = RBX_ERR_UNSUPPORTED;
     if (rc == RBX_OK) {
         SasoArgs<T> a;
         a.ent = ent; a.off = off; a.vec_nnz = (int) vec_nnz; a.nbuckets = nbuckets; a.njb = njb; a.msplit = msplit; a.nchunks = nchunks;
+        a.nrb = nrb; a.dbg_skip = getenv("RBX_SASO_SKIP") ? atoi(getenv("RBX_SASO_SKIP")) : 0;
         a.M = M; a.N = N; a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial;
-        const size_t smem = (size_t) SASO_NST * SASO_MC * SASO_W * sizeof(T) + 2 * SASO_NST * sizeof(uint64_t);
-        static bool attr_set[2] = { false, false };
-        const int ti = sizeof(T) == 8 ? 1 : 0;
-        if (!attr_set[ti]) {
+        SasoStream<T> x;
+        x.X = X; x.ldx = sx_l; x.K = K; x.N = N; x.ent_stride = ent_stride; x.off_stride = off_stride;
+        const size_t smem = (size_t) SASO_NST * (SASO_MC * SASO_W * sizeof(T) + ent_stride * 2 + off_stride * 4);
+        if (smem > 227 * 1024) rc = RBX_ERR_UNSUPPORTED;
+        if (rc == RBX_OK) {
             cudaFuncSetAttribute(saso_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-            attr_set[ti] = true;
+            saso_rows_kernel<T><<<(unsigned)(njb * msplit * nrb), SASO_THREADS, smem, stream>>>(x, a);
+            count_launch();
+            rc = check_launch("saso_rows_kernel");
         }
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)(njb * msplit * nrg * cs));
-        cfg.blockDim = dim3(SASO_THREADS);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = stream;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
-        if (cudaLaunchKernelEx(&cfg, saso_rows_kernel<T>, tmap, a) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
-        count_launch();
-        if (rc == RBX_OK) rc = check_launch("saso_rows_kernel");
         if (rc == RBX_OK && msplit > 1) {
             int64_t blocks = (M * N + 255) / 256;
             if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
