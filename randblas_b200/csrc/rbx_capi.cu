@@ -289,24 +289,9 @@ static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p
     cudaStream_t st = (cudaStream_t) stream;
     // streaming kernel for the SASO hot case; everything else regenerates the triplets and scatters
     if (!s.s_trans && major_axis == 'S' && S_rows <= S_cols) {
-        int rc = RBX_ERR_UNSUPPORTED;
-        if (s.sx_j == 1) {
-            rc = launch_saso_fast<T>(mk_ctr(ctr), mk_key(key), S_rows, S_cols, vec_nnz, ro_s, co_s, s.M, s.N, s.K, alpha,
-                                     A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
-        } else if (s.sx_l == 1 && s.K >= 4096 && s.M <= 4096 && vec_nnz <= 32) {
-            // columns of op(A) are contiguous: re-lay the data with contiguous rows first (one extra read + write of A)
-            const int64_t ldt = (s.N + 1) & ~(int64_t) 1;
-            T* At = nullptr;
-            if (cudaMallocAsync(&At, sizeof(T) * (size_t)(s.K * ldt), st) == cudaSuccess) {
-                rc = launch_transpose<T>(A, s.K, s.N, s.sx_j, At, ldt, st);
-                if (rc == RBX_OK)
-                    rc = launch_saso_fast<T>(mk_ctr(ctr), mk_key(key), S_rows, S_cols, vec_nnz, ro_s, co_s, s.M, s.N, s.K, alpha,
-                                             At, ldt, 1, beta, B, s.sc_i, s.sc_j, st);
-                cudaFreeAsync(At, st);
-            } else {
-                cudaGetLastError();
-            }
-        }
+        // both data layouts are handled natively (rows of op(A) contiguous, or columns contiguous)
+        const int rc = launch_saso_fast<T>(mk_ctr(ctr), mk_key(key), S_rows, S_cols, vec_nnz, ro_s, co_s, s.M, s.N, s.K, alpha,
+                                           A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
         if (rc != RBX_ERR_UNSUPPORTED) return rc;
     }
     RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));
