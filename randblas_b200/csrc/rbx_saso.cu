@@ -5,19 +5,24 @@
 // coo_spmm_impl.hh:79-162): the reference sorts the triplets on the host and makes n passes over them.
 //
 // Design (what was measured on B200 is in DESIGN.md, "SASO kernel"):
-//   * a CTA owns a tile of B, 1024 rows x one 128-byte row segment (16 doubles / 32 floats), resident in SHARED memory
-//     for the whole pass; warp w owns 64 of those rows, so updates need no atomics and no inter-warp ordering;
-//   * A streams through a shared-memory ring in 128-row chunks: cp.async for row-contiguous data, or vector loads + an
-//     XOR-swizzled transposing store for column-contiguous data (the ring layout is the same for both);
-//   * an update is: broadcast-load one 16-bit code, gather 128 B of the A chunk, read-modify-write 128 B of the B tile,
-//     all conflict-free. A double-precision warp instruction carries two entries (one per half-warp);
-//   * the operator is regenerated on the device (bit-exact Fisher-Yates, rbx_fy.cuh) by a prep kernel that buckets the
-//     entries of each 128-column chunk of S by owning warp, in a fixed order => run-to-run identical results;
+//   * a CTA owns a tile of B, 1024 rows x one 128-byte row segment (16 doubles / 32 floats), resident in REGISTERS for
+//     the whole pass: warp w owns 64 rows; a lane owns one column of the segment and (double: its half-warp's) 32 / 64
+//     rows, one accumulator register each;
+//   * A streams through a shared-memory ring in chunks of CK rows (cp.async for row-contiguous data; vector loads and
+//     an XOR-swizzled transposing store for column-contiguous data -- the ring layout is the same for both);
+//   * accumulator registers cannot be indexed dynamically, so the operator is delivered SORTED BY ROW: a prep kernel
+//     regenerates each CK-column chunk of S on the device (bit-exact Fisher-Yates, rbx_fy.cuh), sorts its entries by
+//     (row, column) and emits, per warp, a stream of 32-bit codes (ring byte offset of the A row | sign << 31) plus a
+//     count per accumulator slot. The main loop is a statically unrolled walk over the slots with a dynamic trip count
+//     per slot: one broadcast LDS (code), one 128-byte gather LDS, one FP add. No atomics, no shared-memory
+//     read-modify-write, fixed summation order => run-to-run identical results;
+//   * double precision: the two half-warps work on different rows; the prep kernel pairs their streams and pads the
+//     shorter with a code that points at a zero row of the ring;
 //   * the row blocks (d / 1024) of one column segment are adjacent CTAs and re-read the A chunk through L2, so HBM
 //     sees each byte of A once.
 // Rejected after measurement: TMA boxes for the A chunk (256-byte box rows are TMA row-rate bound, ~28 cycles/row),
-// cluster multicast (73 cycles/row), register-resident tiles selected with brx.idx (~45 issue slots per select).
-// Bound: shared-memory bandwidth (24 B per update) and the L2->SM re-read, not HBM; see DESIGN.md for the arithmetic.
+// cluster multicast (73 cycles/row), register tiles selected with brx.idx (~45 issue slots per select), B tile in
+// shared memory with read-modify-write (latency bound at 16 warps/SM, 24 B of shared-memory traffic per update).
 #include <cstdlib>
 #include "rbx_kernels.cuh"
 #include "rbx_fy.cuh"
@@ -25,103 +30,254 @@
 
 namespace rbx {
 
-constexpr int SASO_MC = 128;        // rows of A per chunk (= columns of S per chunk)
 constexpr int SASO_ROWB = 128;      // bytes of one row segment of A / B handled by a CTA
 constexpr int SASO_WARPS = 16;
 constexpr int SASO_RW = 64;         // rows of B per warp
 constexpr int SASO_R = SASO_WARPS * SASO_RW;   // rows of B per CTA
 constexpr int SASO_THREADS = SASO_WARPS * 32;
-constexpr int SASO_MAXST = 4;       // ring stages (3 when vec_nnz is large)
+constexpr int SASO_NST = 3;         // ring stages
+constexpr int SASO_PAD = 4;         // zero codes after each row block's stream (read-ahead of the main loop)
+constexpr uint32_t SASO_SIGN = 0x80000000u;
+constexpr uint32_t SASO_AMASK = 0x0001FFFFu;
 
-// ---- prep: bucket the entries of each chunk by owning warp ------------------------------------------------
-// ent[chunk * MC * k + off[chunk][b] ...] = 16-bit codes: c_local (7) | r_local (6) << 7 | negative << 13 | valid << 14,
-// in (column, draw) order inside each bucket.
-template <int KMAX>
-__global__ void __launch_bounds__(SASO_MC) saso_prep_kernel(Ctr128 ctr, Key64 key, int vec_nnz, int64_t dim_major, int64_t ro, int64_t co,
-                                                          int64_t M, int64_t K, int nbuckets, int off_stride, uint16_t* __restrict__ ent,
-                                                          uint32_t* __restrict__ off) {
-    extern __shared__ uint16_t sh[];
-    uint16_t* code = sh;                               // MC * vec_nnz
-    uint16_t* bkt = sh + SASO_MC * vec_nnz;            // MC * vec_nnz
-    __shared__ uint32_t cnt[SASO_MC + 1];
+// exclusive scan of in[0..n) into out[0..n], out[n] = total; all SASO_THREADS threads of the block call it
+__device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* out, int n, uint32_t* wtot) {
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int per = (n + SASO_THREADS - 1) / SASO_THREADS;
+    const int b = t * per, e = (b + per < n) ? b + per : n;
+    uint32_t local = 0;
+    for (int i = b; i < e; ++i) local += in[i];
+    uint32_t inc = local;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
+    if (lane == 31) wtot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = lane < SASO_WARPS ? wtot[lane] : 0, winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, winc, d); if (lane >= d) winc += y; }
+        if (lane < SASO_WARPS) wtot[lane] = winc - w;
+        if (lane == SASO_WARPS - 1) out[n] = winc;
+    }
+    __syncthreads();
+    uint32_t run = inc - local + wtot[warp];
+    for (int i = b; i < e; ++i) { const uint32_t v = in[i]; out[i] = run; run += v; }
+    __syncthreads();
+}
+
+// ---- prep: one block per chunk of CK columns of S -----------------------------------------------------------
+// Outputs, per chunk:
+//   stream[chunk * stream_stride + ...]  elements of HALVES codes; element e of slot q is at ws-relative position pos(q)+e
+//   cnt[chunk * cnt_stride + q]          elements in slot q (q = bucket * NS + s; rows bucket*64 + h*NS + s, h < HALVES)
+//   ws[chunk * ws_stride + b]            first element of bucket b (b = 0 .. nbuckets), row blocks start 16-byte aligned
+//                                        and are followed by >= SASO_PAD zero elements
+template <int KMAX, int HALVES>
+__global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key64 key, int vec_nnz, int64_t dim_major, int64_t ro, int64_t co,
+                                                               int64_t M, int64_t K, int CK, int nbuckets, int nrb, int cols_contig,
+                                                               uint32_t* __restrict__ stream, int stream_stride,
+                                                               uint16_t* __restrict__ cnt, int cnt_stride,
+                                                               uint32_t* __restrict__ ws, int ws_stride) {
+    constexpr int NS = SASO_RW / HALVES;
+    extern __shared__ uint32_t sh32[];
+    __shared__ uint32_t wtot[SASO_WARPS];
     const int t = threadIdx.x;
+    const int Mp = nbuckets * SASO_RW, E = CK * vec_nnz, nslots = nbuckets * NS;
+    uint32_t* sorted = sh32;                 // E      codes ordered by (row, column)
+    uint32_t* tcode = sorted + E;            // E      codes in generation order
+    uint32_t* rowoff = tcode + E;            // Mp + 1
+    uint32_t* rowcnt = rowoff + Mp + 1;      // Mp
+    uint32_t* slotcnt = rowcnt + Mp;         // nslots
+    uint32_t* slotoff = slotcnt + nslots;    // nslots + 1
+    uint16_t* trow = reinterpret_cast<uint16_t*>(slotoff + nslots + 1);   // E
     const int64_t chunk = blockIdx.x;
-    const int64_t l = chunk * SASO_MC + t;
-    for (int j = 0; j < vec_nnz; ++j) bkt[t * vec_nnz + j] = 0xFFFF;
-    if (l < K) {
+    const uint32_t zero_code = (uint32_t) CK * SASO_ROWB;
+
+    uint32_t* so = stream + chunk * stream_stride;
+    for (int e = t; e < stream_stride; e += SASO_THREADS) so[e] = zero_code;
+    for (int r = t; r < Mp; r += SASO_THREADS) rowcnt[r] = 0;
+    for (int e = t; e < E; e += SASO_THREADS) trow[e] = 0xFFFF;
+    __syncthreads();
+    const int64_t l = chunk * CK + t;
+    if (t < CK && l < K) {
+        const uint32_t c = (uint32_t) t;
+        // ring offset of row c; column-contiguous data sits XOR-swizzled by (c mod W) elements (see saso_tile_kernel)
+        const uint32_t base = c * SASO_ROWB | (cols_contig ? (c & (uint32_t)(32 / HALVES - 1)) * (4u * HALVES) : 0u);
         fy_vector<KMAX>(ctr, key, co + l, vec_nnz, dim_major, [&](int j, int64_t idx, bool negative) {
             const int64_t r = idx - ro;
             if (r >= 0 && r < M) {
-                code[t * vec_nnz + j] = (uint16_t)(t | ((int)(r % SASO_RW) << 7) | (negative ? 1 << 13 : 0) | (1 << 14));
-                bkt[t * vec_nnz + j] = (uint16_t)(r / SASO_RW);
+                tcode[t * vec_nnz + j] = base | (negative ? SASO_SIGN : 0u);
+                trow[t * vec_nnz + j] = (uint16_t) r;
+                atomicAdd(&rowcnt[r], 1u);
             }
         });
     }
     __syncthreads();
-    const int total = SASO_MC * vec_nnz;
-    uint32_t mine = 0;
-    if (t < nbuckets)
-        for (int e = 0; e < total; ++e) mine += (bkt[e] == t);
-    if (t < nbuckets) cnt[t + 1] = mine;
-    if (t == 0) cnt[0] = 0;
+    block_excl_scan(rowcnt, rowoff, Mp, wtot);
+    for (int r = t; r < Mp; r += SASO_THREADS) rowcnt[r] = 0;
     __syncthreads();
-    if (t == 0) for (int b = 0; b < nbuckets; ++b) cnt[b + 1] += cnt[b];
+    for (int e = t; e < E; e += SASO_THREADS) {
+        const uint32_t r = trow[e];
+        if (r != 0xFFFF) sorted[rowoff[r] + atomicAdd(&rowcnt[r], 1u)] = tcode[e];
+    }
     __syncthreads();
-    uint32_t* o = off + chunk * off_stride;
-    for (int b = t; b < off_stride; b += SASO_MC) o[b] = cnt[b <= nbuckets ? b : nbuckets];
-    if (t < nbuckets) {
-        uint16_t* dst = ent + chunk * total + cnt[t];
-        for (int e = 0; e < total; ++e)
-            if (bkt[e] == t) *dst++ = code[e];
+    // fixed order inside a row (by column): the scatter above is in arrival order
+    for (int r = t; r < Mp; r += SASO_THREADS) {
+        uint32_t* s = sorted + rowoff[r];
+        const int n = (int) rowcnt[r];
+        for (int i = 1; i < n; ++i) {
+            const uint32_t v = s[i];
+            int k = i - 1;
+            while (k >= 0 && (s[k] & ~SASO_SIGN) > (v & ~SASO_SIGN)) { s[k + 1] = s[k]; --k; }
+            s[k + 1] = v;
+        }
+    }
+    for (int q = t; q < nslots; q += SASO_THREADS) {
+        const int b = q / NS, s = q % NS;
+        uint32_t n = 0;
+#pragma unroll
+        for (int h = 0; h < HALVES; ++h) { const uint32_t v = rowcnt[b * SASO_RW + h * NS + s]; n = v > n ? v : n; }
+        slotcnt[q] = n;
+    }
+    __syncthreads();
+    block_excl_scan(slotcnt, slotoff, nslots, wtot);
+    // shift of each row block: aligned start, SASO_PAD zero elements after the previous block
+    uint32_t shift[4] = { 0, 0, 0, 0 };
+    for (int rb = 1; rb < nrb; ++rb) {
+        const uint32_t raw = slotoff[rb * SASO_WARPS * NS];
+        shift[rb] = ((raw + shift[rb - 1] + SASO_PAD + 3u) & ~3u) - raw;
+    }
+    uint16_t* co_ = cnt + chunk * cnt_stride;
+    for (int q = t; q < cnt_stride; q += SASO_THREADS) co_[q] = q < nslots ? (uint16_t) slotcnt[q] : (uint16_t) 0;
+    uint32_t* wo = ws + chunk * ws_stride;
+    for (int b = t; b <= nbuckets; b += SASO_THREADS) {
+        const int rb = b < nbuckets ? b / SASO_WARPS : nrb - 1;
+        wo[b] = slotoff[b * NS] + shift[rb];
+    }
+    for (int q = t; q < nslots; q += SASO_THREADS) {
+        const int b = q / NS, s = q % NS;
+        const uint32_t n = slotcnt[q], p = slotoff[q] + shift[b / SASO_WARPS];
+#pragma unroll
+        for (int h = 0; h < HALVES; ++h) {
+            const int row = b * SASO_RW + h * NS + s;
+            const uint32_t nr = rowcnt[row];
+            const uint32_t* src = sorted + rowoff[row];
+            for (uint32_t i = 0; i < nr; ++i) so[(p + i) * HALVES + h] = src[i];
+        }
+        (void) n;
     }
 }
 
 template <typename T>
 struct SasoArgs {
     const T* X; int64_t sx_l, sx_j; int64_t K, N;      // data view: X[l * sx_l + j * sx_j], one of the strides is 1
-    const uint16_t* ent; const uint32_t* off;
-    int ent_stride, off_stride;                        // codes / uint32 per chunk
-    int nbuckets, njb, nrb, msplit, nchunks, nst, dbg_skip;
+    const uint32_t* stream; const uint16_t* cnt; const uint32_t* ws;
+    int stream_stride, cnt_stride, ws_stride;
+    int CK, cap;                                       // rows per chunk; stream elements a ring stage can hold
+    int nbuckets, njb, nrb, msplit, nchunks, dbg_skip;
     int64_t M;
     T alpha, beta;
     T* C; int64_t sc_i, sc_j;
     T* partial;                                        // [msplit][M][njb * W] when msplit > 1
 };
 
-template <typename T> __device__ __forceinline__ T flip_sign(T v, uint32_t neg);
-template <> __device__ __forceinline__ double flip_sign<double>(double v, uint32_t neg) {
-    return __hiloint2double(__double2hiint(v) ^ (int)(neg << 31), __double2loint(v));
+// asynchronous global->shared copies; bytes beyond src_bytes are zero-filled (ragged edges)
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
-template <> __device__ __forceinline__ float flip_sign<float>(float v, uint32_t neg) {
-    return __int_as_float(__float_as_int(v) ^ (int)(neg << 31));
-}
-
-// 16-byte asynchronous global->shared copy; bytes beyond src_bytes are zero-filled (ragged edges)
-__device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+template <int BYTES> __device__ __forceinline__ void cp_async_small(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" :: "r"(dst), "l"(src), "n"(BYTES), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-// Ring layout of one A chunk: row c is 128 bytes; its 16-byte pieces are XOR-swizzled with (c >> 1) & 7 so that both the
-// gather (lanes along the row) and the transposing store of column-contiguous data (lanes along c) spread over the banks.
-__device__ __forceinline__ uint32_t ring_offset(uint32_t c, uint32_t byte_in_row) {
-    return c * SASO_ROWB + ((((byte_in_row >> 4) ^ (c >> 1)) & 7u) << 4) + (byte_in_row & 15u);
+// acc += (i < n) ? (+/-) *(T*)addr : 0, sign taken from bit 31 of code; a predicated load, no branch
+template <typename T> __device__ __forceinline__ void gather_add_if(T& acc, uint32_t addr, uint32_t code, int n, int i);
+template <> __device__ __forceinline__ void gather_add_if<double>(double& acc, uint32_t addr, uint32_t code, int n, int i) {
+    unsigned long long bits;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.gt.s32 p, %2, %3;\n\tmov.b64 %0, 0;\n\t@p ld.shared.b64 %0, [%1];\n\t}"
+                 : "=l"(bits) : "r"(addr), "r"(n), "r"(i));
+    const double v = __longlong_as_double((long long) bits);
+    acc += __hiloint2double(__double2hiint(v) ^ (int)(code & SASO_SIGN), __double2loint(v));
+}
+template <> __device__ __forceinline__ void gather_add_if<float>(float& acc, uint32_t addr, uint32_t code, int n, int i) {
+    uint32_t bits;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.gt.s32 p, %2, %3;\n\tmov.b32 %0, 0;\n\t@p ld.shared.b32 %0, [%1];\n\t}"
+                 : "=r"(bits) : "r"(addr), "r"(n), "r"(i));
+    acc += __uint_as_float(bits ^ (code & SASO_SIGN));
+}
+template <typename T> __device__ __forceinline__ T lds_signed(uint32_t addr, uint32_t code);
+template <> __device__ __forceinline__ double lds_signed<double>(uint32_t addr, uint32_t code) {
+    double v;
+    asm volatile("{\n\t.reg .b32 lo, hi;\n\tld.shared.v2.b32 {lo, hi}, [%1];\n\tlop3.b32 hi, hi, %2, 0x80000000, 0x78;\n\tmov.b64 %0, {lo, hi};\n\t}"
+                 : "=d"(v) : "r"(addr), "r"(code));
+    return v;
+}
+template <> __device__ __forceinline__ float lds_signed<float>(uint32_t addr, uint32_t code) {
+    float v;
+    asm volatile("{\n\t.reg .b32 x;\n\tld.shared.b32 x, [%1];\n\tlop3.b32 x, x, %2, 0x80000000, 0x78;\n\tmov.b32 %0, x;\n\t}"
+                 : "=f"(v) : "r"(addr), "r"(code));
+    return v;
+}
+// volatile: keeps the code loads where they are written (one slot ahead of their use) instead of all up front
+__device__ __forceinline__ uint32_t ld_code(const uint32_t* p, bool in_smem) {
+    uint32_t v;
+    if (in_smem) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
+    else asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+constexpr int SASO_NU = 3;          // elements of a slot handled by predicated straight-line code; the rest loop
+
+// slots [0, NS) of this warp: acc[s] += sum of the gathered (signed) A values of its elements.
+// codes: this lane's first code (step = codes per element); abase: shared address of the stage's A chunk.
+template <typename T, int NS, bool IN_SMEM>
+__device__ __forceinline__ void saso_consume(T (&acc)[NS], const uint32_t* codes, int step, uint32_t abase, uint32_t lx, const uint16_t* cnts) {
+    uint32_t c[SASO_NU];
+#pragma unroll
+    for (int i = 0; i < SASO_NU; ++i) c[i] = ld_code(codes + i * step, IN_SMEM);
+#pragma unroll
+    for (int g = 0; g < NS; g += 8) {
+        const uint4 cq = *reinterpret_cast<const uint4*>(cnts + g);
+        const uint32_t cw[4] = { cq.x, cq.y, cq.z, cq.w };
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int n = (int)((cw[e >> 1] >> (16 * (e & 1))) & 0xffffu);
+            uint32_t addr[SASO_NU], cc[SASO_NU];
+#pragma unroll
+            for (int i = 0; i < SASO_NU; ++i) { cc[i] = c[i]; addr[i] = abase + ((c[i] & SASO_AMASK) ^ lx); }
+            const uint32_t* cur = codes;
+            codes += n * step;
+#pragma unroll
+            for (int i = 0; i < SASO_NU; ++i) c[i] = ld_code(codes + i * step, IN_SMEM);       // next slot's codes
+#pragma unroll
+            for (int i = 0; i < SASO_NU; ++i) gather_add_if<T>(acc[g + e], addr[i], cc[i], n, i);
+            if (n > SASO_NU) {
+#pragma unroll 1
+                for (int i = SASO_NU; i < n; ++i) {
+                    const uint32_t code = ld_code(cur + i * step, IN_SMEM);
+                    acc[g + e] += lds_signed<T>(abase + ((code & SASO_AMASK) ^ lx), code);
+                }
+            }
+        }
+    }
 }
 
 // COLS_CONTIG: columns of the data view are contiguous (sx_l == 1); otherwise rows are (sx_j == 1).
+// Ring layout of one A chunk: row c is 128 bytes at offset c * 128. Row-contiguous data is copied as is (16-byte
+// cp.async); column-contiguous data is copied element by element (8 / 4-byte cp.async, lanes run down a column) to
+// position jj ^ (c mod W) of row c, which spreads both that transposing write and the gather over all banks.
 template <typename T, bool COLS_CONTIG>
 __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoArgs<T> a) {
     constexpr int W = SASO_ROWB / (int) sizeof(T);     // columns per CTA: 16 doubles / 32 floats
-    constexpr int EPW = 32 / W;                        // entries per warp instruction: 2 / 1
+    constexpr int HALVES = 32 / W;                     // entries per warp instruction: 2 / 1
+    constexpr int NS = SASO_RW / HALVES;               // accumulators per lane: 32 doubles / 64 floats
     constexpr int EP = 16 / (int) sizeof(T);           // elements per 16-byte piece
-    constexpr int A_BYTES = SASO_MC * SASO_ROWB;
+    constexpr int CNT_BYTES = SASO_WARPS * NS * 2;
     extern __shared__ __align__(128) uint8_t smem[];
-    T* Bs = reinterpret_cast<T*>(smem);                                   // [SASO_R][W]
-    uint8_t* stages = smem + (size_t) SASO_R * SASO_ROWB;
-    const int ent_bytes = a.ent_stride * 2, off_bytes = a.off_stride * 4;
-    const int stage_bytes = A_BYTES + ent_bytes + off_bytes;
-    const int nst = a.nst;
+    const uint32_t smem0 = smem_u32(smem);
+    const int CK = a.CK;
+    const int a_bytes = CK * SASO_ROWB;
+    const int stage_bytes = a_bytes + SASO_ROWB + CNT_BYTES + a.cap * HALVES * 4;   // A | zero row | counts | codes
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int sub = lane / W, jl = lane % W;
@@ -134,122 +290,98 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     const int cb = ms * per;
     const int ce = (cb + per < a.nchunks) ? cb + per : a.nchunks;
     const int64_t j0 = (int64_t) jb * W;
+    const int b_first = rb * SASO_WARPS;
+    const int b_last = (b_first + SASO_WARPS < a.nbuckets) ? b_first + SASO_WARPS : a.nbuckets;
+    const int bucket = b_first + warp;                 // warp owns rows [bucket*64, bucket*64+64) of the window
+    const bool active = bucket < a.nbuckets;
 
-    for (int e = tid; e < SASO_R * SASO_ROWB / 16; e += SASO_THREADS) reinterpret_cast<uint4*>(smem)[e] = make_uint4(0, 0, 0, 0);
+    if (tid < SASO_NST * (SASO_ROWB / 16))             // the zero rows of the stages
+        *reinterpret_cast<uint4*>(smem + (size_t)(tid / (SASO_ROWB / 16)) * stage_bytes + a_bytes + (tid % (SASO_ROWB / 16)) * 16) = make_uint4(0, 0, 0, 0);
 
-    // operator codes + bucket offsets of chunk ch -> stage s (both layouts), and the A chunk when rows are contiguous
-    auto load_async = [&](int ch, int s) {
-        uint8_t* st = stages + (size_t) s * stage_bytes;
+    // A chunk, slot counts and codes of chunk ch -> stage s; [lo, hi) = the row block's range of the code stream
+    auto load_async = [&](int ch, int s, uint32_t lo, uint32_t hi) {
+        const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
         if (!COLS_CONTIG) {
-            for (int p = tid; p < SASO_MC * 8; p += SASO_THREADS) {
+            for (int p = tid; p < CK * 8; p += SASO_THREADS) {
                 const int row = p >> 3, q = p & 7;
-                const int64_t l = (int64_t) ch * SASO_MC + row, col = j0 + (int64_t) q * EP;
+                const int64_t l = (int64_t) ch * CK + row, col = j0 + (int64_t) q * EP;
                 int64_t nb = (l < a.K) ? (a.N - col) * (int64_t) sizeof(T) : 0;
                 nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
                 const T* src = nb > 0 ? a.X + l * a.sx_l + col : a.X;
-                cp_async16(st + ring_offset(row, q * 16), src, (uint32_t) nb);
+                cp_async16(st + p * 16, src, (uint32_t) nb);
+            }
+        } else if (tid < CK) {
+            const int64_t l = (int64_t) ch * CK + tid;
+            const T* src = a.X + (l < a.K ? l : 0) + j0 * a.sx_j;
+            const uint32_t row = st + tid * SASO_ROWB;
+#pragma unroll 8
+            for (int jj = 0; jj < W; ++jj) {
+                const uint32_t nb = (l < a.K && j0 + jj < a.N) ? (uint32_t) sizeof(T) : 0u;
+                cp_async_small<(int) sizeof(T)>(row + ((jj ^ (tid & (W - 1))) * (int) sizeof(T)), nb ? src + jj * a.sx_j : a.X, nb);
             }
         }
-        const uint8_t* esrc = reinterpret_cast<const uint8_t*>(a.ent + (size_t) ch * a.ent_stride);
-        for (int p = tid; p < ent_bytes / 16; p += SASO_THREADS) cp_async16(st + A_BYTES + p * 16, esrc + p * 16, 16);
-        const uint8_t* osrc = reinterpret_cast<const uint8_t*>(a.off + (size_t) ch * a.off_stride);
-        for (int p = tid; p < off_bytes / 16; p += SASO_THREADS) cp_async16(st + A_BYTES + ent_bytes + p * 16, osrc + p * 16, 16);
+        const uint8_t* csrc = reinterpret_cast<const uint8_t*>(a.cnt + (size_t) ch * a.cnt_stride + (size_t) rb * SASO_WARPS * NS);
+        if (tid < CNT_BYTES / 16) cp_async16(st + a_bytes + SASO_ROWB + tid * 16, csrc + tid * 16, 16);
+        uint32_t nel = hi + SASO_PAD - lo;
+        nel = nel > (uint32_t) a.cap ? (uint32_t) a.cap : nel;
+        const int npiece = (int)((nel * HALVES * 4 + 15) / 16);
+        const uint8_t* ssrc = reinterpret_cast<const uint8_t*>(a.stream + (size_t) ch * a.stream_stride + (size_t) lo * HALVES);
+        const uint32_t sdst = st + a_bytes + SASO_ROWB + CNT_BYTES;
+        for (int p = tid; p < npiece; p += SASO_THREADS) cp_async16(sdst + p * 16, ssrc + p * 16, 16);
     };
-    // column-contiguous data: 16-byte vector loads down the columns into registers ...
-    constexpr int PPC = SASO_MC / EP;                  // pieces per column
-    constexpr int NPIECE = W * PPC / SASO_THREADS;     // = 2
-    T regs[NPIECE][EP];
-    auto load_cols = [&](int ch) {
-#pragma unroll
-        for (int i = 0; i < NPIECE; ++i) {
-            const int p = tid + i * SASO_THREADS, jj = p / PPC, c0 = (p % PPC) * EP;
-            const int64_t l = (int64_t) ch * SASO_MC + c0, col = j0 + jj;
-            const T* src = a.X + l + col * a.sx_j;
-            if (col < a.N && l + EP <= a.K) {
-                const uint4 v = __ldcs(reinterpret_cast<const uint4*>(src));
-                *reinterpret_cast<uint4*>(regs[i]) = v;
-            } else {
-#pragma unroll
-                for (int q = 0; q < EP; ++q) regs[i][q] = (col < a.N && l + q < a.K) ? src[q] : (T) 0;
-            }
-        }
-    };
-    // ... and an element-wise transposing store into the swizzled ring rows
-    auto store_cols = [&](int s) {
-        uint8_t* st = stages + (size_t) s * stage_bytes;
-#pragma unroll
-        for (int i = 0; i < NPIECE; ++i) {
-            const int p = tid + i * SASO_THREADS, jj = p / PPC, c0 = (p % PPC) * EP;
-#pragma unroll
-            for (int q = 0; q < EP; ++q) *reinterpret_cast<T*>(st + ring_offset(c0 + q, jj * (int) sizeof(T))) = regs[i][q];
-        }
-    };
+    auto ws_at = [&](int ch, int b) -> uint32_t { return ch < ce ? __ldg(a.ws + (size_t) ch * a.ws_stride + b) : 0u; };
 
-    const int dist = COLS_CONTIG ? 2 : nst - 1;        // prefetch distance in chunks
-    for (int s = 0; s < dist; ++s) {
-        if (cb + s < ce) {
-            load_async(cb + s, s);
-            if (COLS_CONTIG) { load_cols(cb + s); store_cols(s); }
-        }
+    constexpr int DIST = SASO_NST - 1;                 // prefetch distance in chunks
+    for (int s = 0; s < DIST; ++s) {
+        if (cb + s < ce) load_async(cb + s, s, ws_at(cb + s, b_first), ws_at(cb + s, b_last));
         cp_async_commit();
     }
+    // stream positions, fetched one iteration ahead of their use
+    uint32_t pf_lo = ws_at(cb + DIST, b_first), pf_hi = ws_at(cb + DIST, b_last);            // for the next prefetch
+    uint32_t my_lo = ws_at(cb, b_first), my_first = 0, my_end = 0;                             // for the chunk being consumed
+    if (active) { my_first = ws_at(cb, bucket); my_end = ws_at(cb, bucket + 1); }
 
-    const int bucket = rb * SASO_WARPS + warp;          // warp owns rows [bucket*64, bucket*64+64) of the window
-    const bool active = bucket < a.nbuckets;
-    T* bwarp = Bs + (size_t) warp * SASO_RW * W + jl;
+    T acc[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) acc[s] = (T) 0;
+    const uint32_t lx = (uint32_t) jl * (uint32_t) sizeof(T);
 
     for (int ch = cb, it = 0; ch < ce; ++ch, ++it) {
-        if (dist >= 3) cp_async_wait<2>(); else cp_async_wait<1>();
+        cp_async_wait<DIST - 1>();
         __syncthreads();                                // chunk `it` has landed; everyone is done with chunk it-1
-        const int nxt = ch + dist;
-        if (nxt < ce) { load_async(nxt, (it + dist) % nst); if (COLS_CONTIG) load_cols(nxt); }
+        const int nxt = ch + DIST;
+        if (nxt < ce) load_async(nxt, (it + DIST) % SASO_NST, pf_lo, pf_hi);
         cp_async_commit();
+        pf_lo = ws_at(nxt + 1, b_first); pf_hi = ws_at(nxt + 1, b_last);
+        const uint32_t lo = my_lo, first = my_first, end = my_end;
+        my_lo = ws_at(ch + 1, b_first);
+        if (active) { my_first = ws_at(ch + 1, bucket); my_end = ws_at(ch + 1, bucket + 1); }
         if (active && a.dbg_skip != 1) {
-            const uint8_t* st8 = stages + (size_t)(it % nst) * stage_bytes;
-            const uint16_t* ents = reinterpret_cast<const uint16_t*>(st8 + A_BYTES);
-            const uint32_t* offs = reinterpret_cast<const uint32_t*>(st8 + A_BYTES + ent_bytes);
-            const uint32_t o0 = offs[bucket], o1 = offs[bucket + 1];
-            for (uint32_t base = o0; base < o1; base += 2 * EPW) {
-                uint32_t r[2]; T w[2]; bool ok[2];
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const uint32_t idx = base + u * EPW + sub;
-                    ok[u] = idx < o1;
-                    const uint32_t e = ok[u] ? ents[idx] : 0u;
-                    const T v = *reinterpret_cast<const T*>(st8 + ring_offset(e & 127u, jl * (int) sizeof(T)));
-                    w[u] = ok[u] ? flip_sign<T>(v, (e >> 13) & 1u) : (T) 0;
-                    r[u] = (e >> 7) & 63u;
-                }
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    T* b = bwarp + r[u] * W;
-                    if (EPW == 2) {
-                        // the two half-warps carry different entries; if both hit the same row they must not race
-                        const uint32_t other = __shfl_xor_sync(0xffffffffu, ok[u] ? r[u] : 0xffu, 16);
-                        const bool clash = ok[u] && other == r[u];
-                        if (!clash) { if (ok[u]) *b += w[u]; }
-                        else { if (sub == 0) *b += w[u]; __syncwarp(); if (sub == 1) *b += w[u]; __syncwarp(); }
-                    } else {
-                        if (ok[u]) *b += w[u];
-                    }
-                }
+            const uint32_t st = smem0 + (uint32_t)(it % SASO_NST) * stage_bytes;
+            const uint8_t* st8 = smem + (size_t)(it % SASO_NST) * stage_bytes;
+            const uint16_t* cnts = reinterpret_cast<const uint16_t*>(st8 + a_bytes + SASO_ROWB) + warp * NS;
+            if (end + SASO_PAD - lo <= (uint32_t) a.cap) {
+                const uint32_t* codes = reinterpret_cast<const uint32_t*>(st8 + a_bytes + SASO_ROWB + CNT_BYTES) + (size_t)(first - lo) * HALVES + sub;
+                saso_consume<T, NS, true>(acc, codes, HALVES, st, lx, cnts);
+            } else {
+                // the stage could not hold this warp's codes (far tail of the distribution): read them from global memory
+                const uint32_t* codes = a.stream + (size_t) ch * a.stream_stride + (size_t) first * HALVES + sub;
+                saso_consume<T, NS, false>(acc, codes, HALVES, st, lx, cnts);
             }
         }
-        if (COLS_CONTIG && nxt < ce) store_cols((it + dist) % nst);
     }
     cp_async_wait<0>();
-    __syncthreads();
     if (active) {
         const int64_t col = j0 + jl;
-        for (int i = sub; i < SASO_RW; i += EPW) {
-            const int64_t row = (int64_t) bucket * SASO_RW + i;
-            const T acc = bwarp[i * W];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            const int64_t row = (int64_t) bucket * SASO_RW + sub * NS + s;
             if (row < a.M && col < a.N) {
                 if (a.msplit == 1) {
                     T* c = a.C + row * a.sc_i + col * a.sc_j;
-                    *c = (a.beta == (T) 0) ? a.alpha * acc : a.alpha * acc + a.beta * (*c);
+                    *c = (a.beta == (T) 0) ? a.alpha * acc[s] : a.alpha * acc[s] + a.beta * (*c);
                 } else {
-                    a.partial[((size_t) ms * a.M + row) * ((size_t) a.njb * W) + col] = acc;
+                    a.partial[((size_t) ms * a.M + row) * ((size_t) a.njb * W) + col] = acc[s];
                 }
             }
         }
@@ -275,61 +407,77 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
                      T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
     (void) S_cols;
     constexpr int W = SASO_ROWB / (int) sizeof(T);
+    constexpr int HALVES = 32 / W;
+    constexpr int NS = SASO_RW / HALVES;
+    constexpr size_t SMEM_MAX = 227 * 1024;
     // envelope of this kernel; everything else goes to the general path
     const bool cols_contig = (sx_l == 1 && sx_j != 1);
     if (!cols_contig && sx_j != 1) return RBX_ERR_UNSUPPORTED;
-    if (vec_nnz > 32 || M > SASO_RW * SASO_MC || M < 1 || N < 1 || K < SASO_MC) return RBX_ERR_UNSUPPORTED;
+    if (vec_nnz > 32 || M > 4 * SASO_R || M < 1 || N < 1 || K < 64) return RBX_ERR_UNSUPPORTED;
     const int64_t ld = cols_contig ? sx_j : sx_l;
     if (reinterpret_cast<uintptr_t>(X) % 16 != 0 || (ld * (int64_t) sizeof(T)) % 16 != 0) return RBX_ERR_UNSUPPORTED;
-    if (K > (int64_t) 0x7fffffff - SASO_MC || N > 0x7fffffff) return RBX_ERR_UNSUPPORTED;
+    if (K > (int64_t) 0x7fffffff - 512 || N > 0x7fffffff) return RBX_ERR_UNSUPPORTED;
     if (alpha == (T) 0) return launch_scale_view<T>(C, M, N, sc_i, sc_j, beta, stream);
 
-    const int nbuckets = (int)((M + SASO_RW - 1) / SASO_RW);            // <= 128 == threads of the prep kernel
+    const int nbuckets = (int)((M + SASO_RW - 1) / SASO_RW);
     const int nrb = (nbuckets + SASO_WARPS - 1) / SASO_WARPS;           // row blocks of 1024 rows
     const int njb = (int)((N + W - 1) / W);
-    const int nchunks = (int)((K + SASO_MC - 1) / SASO_MC);
+    // rows of A per chunk: as many as three ring stages (A chunk + the codes that go with it) fit in shared memory
+    int CK = 0, cap = 0;
+    size_t stage = 0;
+    for (int ck = 512; ck >= 64; ck -= 64) {
+        const double ent_rb = (double) ck * (double) vec_nnz * (double)(M < SASO_R ? M : SASO_R) / (double) S_rows;
+        const int c = (((int)(HALVES == 2 ? ent_rb : 1.25 * ent_rb) + 64) + 31) & ~31;
+        const size_t sb = (size_t) ck * SASO_ROWB + SASO_ROWB + SASO_WARPS * NS * 2 + (size_t) c * HALVES * 4;
+        if (SASO_NST * sb <= SMEM_MAX && (int64_t) ck <= ((K + 63) & ~(int64_t) 63)) { CK = ck; cap = c; stage = sb; break; }
+    }
+    if (CK == 0) return RBX_ERR_UNSUPPORTED;
+    const int nchunks = (int)((K + CK - 1) / CK);
+    const int E = CK * (int) vec_nnz, Mp = nbuckets * SASO_RW, nslots = nbuckets * NS;
+    const size_t prep_smem = (size_t) E * 10 + (size_t)(2 * Mp + 2 * nslots + 2) * 4 + 16;
+    if (prep_smem > SMEM_MAX) return RBX_ERR_UNSUPPORTED;
     // split the contraction axis so that the grid is several waves of CTAs (one CTA per SM)
     int msplit = (6 * kNumSMs + njb * nrb - 1) / (njb * nrb);
-    if (msplit > nchunks / 16) msplit = nchunks / 16;
+    if (msplit > nchunks / 8) msplit = nchunks / 8;
     if (msplit < 1) msplit = 1;
     if (const char* ev = getenv("RBX_SASO_MSPLIT")) { const int v = atoi(ev); if (v >= 1 && v <= nchunks) msplit = v; }
 
-    const int ent_stride = SASO_MC * (int) vec_nnz;                     // a multiple of 128 codes => 16-byte multiple
-    const int off_stride = (nbuckets + 1 + 3) & ~3;
-    const size_t stage = (size_t) SASO_MC * SASO_ROWB + ent_stride * 2 + off_stride * 4;
-    int nst = SASO_MAXST;
-    while (nst > 3 && (size_t) SASO_R * SASO_ROWB + nst * stage > 227 * 1024) --nst;
-    const size_t smem = (size_t) SASO_R * SASO_ROWB + nst * stage;
-    if (smem > 227 * 1024) return RBX_ERR_UNSUPPORTED;
-
-    uint16_t* ent = nullptr; uint32_t* off = nullptr; T* partial = nullptr;
-    const size_t ent_bytes = (size_t) nchunks * ent_stride * sizeof(uint16_t);
-    const size_t off_bytes = (size_t) nchunks * off_stride * sizeof(uint32_t);
+    const int stream_stride = ((E + nrb * 8 + SASO_PAD) * HALVES + 3) & ~3;      // codes per chunk
+    const int cnt_stride = nrb * SASO_WARPS * NS;
+    const int ws_stride = (nbuckets + 1 + 3) & ~3;
+    uint32_t* codes = nullptr; uint16_t* cnt = nullptr; uint32_t* ws = nullptr; T* partial = nullptr;
     const size_t Np = (size_t) njb * W;
     const size_t part_bytes = msplit > 1 ? (size_t) msplit * M * Np * sizeof(T) : 0;
-    if (cudaMallocAsync(&ent, ent_bytes, stream) != cudaSuccess || cudaMallocAsync(&off, off_bytes, stream) != cudaSuccess ||
+    if (cudaMallocAsync(&codes, (size_t) nchunks * stream_stride * 4, stream) != cudaSuccess ||
+        cudaMallocAsync(&cnt, (size_t) nchunks * cnt_stride * 2, stream) != cudaSuccess ||
+        cudaMallocAsync(&ws, (size_t) nchunks * ws_stride * 4, stream) != cudaSuccess ||
         (part_bytes && cudaMallocAsync(&partial, part_bytes, stream) != cudaSuccess)) {
         cudaGetLastError();
-        if (ent) cudaFreeAsync(ent, stream);
-        if (off) cudaFreeAsync(off, stream);
+        if (codes) cudaFreeAsync(codes, stream);
+        if (cnt) cudaFreeAsync(cnt, stream);
+        if (ws) cudaFreeAsync(ws, stream);
         return RBX_ERR_ALLOC;
     }
     int rc = RBX_OK;
     {
-        const size_t sh = (size_t) SASO_MC * vec_nnz * 2 * sizeof(uint16_t);
-        if (vec_nnz <= 8) saso_prep_kernel<8><<<nchunks, SASO_MC, sh, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, nbuckets, off_stride, ent, off);
-        else              saso_prep_kernel<32><<<nchunks, SASO_MC, sh, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, nbuckets, off_stride, ent, off);
+        auto kern = vec_nnz <= 8 ? saso_prep_kernel<8, HALVES> : saso_prep_kernel<32, HALVES>;
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) prep_smem);
+        kern<<<nchunks, SASO_THREADS, prep_smem, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, CK, nbuckets, nrb, cols_contig ? 1 : 0,
+                                                           codes, stream_stride, cnt, cnt_stride, ws, ws_stride);
         count_launch();
         rc = check_launch("saso_prep_kernel");
     }
     if (rc == RBX_OK) {
         SasoArgs<T> a;
         a.X = X; a.sx_l = sx_l; a.sx_j = sx_j; a.K = K; a.N = N;
-        a.ent = ent; a.off = off; a.ent_stride = ent_stride; a.off_stride = off_stride;
-        a.nbuckets = nbuckets; a.njb = njb; a.nrb = nrb; a.msplit = msplit; a.nchunks = nchunks; a.nst = nst;
+        a.stream = codes; a.cnt = cnt; a.ws = ws;
+        a.stream_stride = stream_stride; a.cnt_stride = cnt_stride; a.ws_stride = ws_stride;
+        a.CK = CK; a.cap = cap;
+        a.nbuckets = nbuckets; a.njb = njb; a.nrb = nrb; a.msplit = msplit; a.nchunks = nchunks;
         a.dbg_skip = getenv("RBX_SASO_SKIP") ? atoi(getenv("RBX_SASO_SKIP")) : 0;
         a.M = M; a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial;
         const unsigned grid = (unsigned)(njb * msplit * nrb);
+        const size_t smem = SASO_NST * stage;
         if (cols_contig) {
             cudaFuncSetAttribute(saso_tile_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
             saso_tile_kernel<T, true><<<grid, SASO_THREADS, smem, stream>>>(a);
@@ -347,7 +495,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
             rc = check_launch("saso_reduce_kernel");
         }
     }
-    cudaFreeAsync(ent, stream); cudaFreeAsync(off, stream);
+    cudaFreeAsync(codes, stream); cudaFreeAsync(cnt, stream); cudaFreeAsync(ws, stream);
     if (partial) cudaFreeAsync(partial, stream);
     return rc;
 }
