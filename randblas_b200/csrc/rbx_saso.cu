@@ -38,7 +38,6 @@ constexpr int SASO_THREADS = SASO_WARPS * 32;
 constexpr int SASO_NST = 3;         // ring stages
 constexpr int SASO_PAD = 4;         // zero codes after each row block's stream (read-ahead of the main loop)
 constexpr uint32_t SASO_SIGN = 0x80000000u;
-constexpr uint32_t SASO_AMASK = 0x0001FFFFu;
 
 // exclusive scan of in[0..n) into out[0..n], out[n] = total; all SASO_THREADS threads of the block call it
 __device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* out, int n, uint32_t* wtot) {
@@ -90,7 +89,10 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     uint32_t* slotoff = slotcnt + nslots;    // nslots + 1
     uint16_t* trow = reinterpret_cast<uint16_t*>(slotoff + nslots + 1);   // E
     const int64_t chunk = blockIdx.x;
-    const uint32_t zero_code = (uint32_t) CK * SASO_ROWB;
+    // a code is the ring offset of A row c in elements: c * (row pitch / sizeof(T)); the pitch is 128 bytes, plus one
+    // element when the data is column-contiguous (see saso_tile_kernel). Row CK of the ring is all zeros.
+    const uint32_t pitch_el = 32u / HALVES + (cols_contig ? 1u : 0u);
+    const uint32_t zero_code = (uint32_t) CK * pitch_el;
 
     uint32_t* so = stream + chunk * stream_stride;
     for (int e = t; e < stream_stride; e += SASO_THREADS) so[e] = zero_code;
@@ -100,8 +102,7 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     const int64_t l = chunk * CK + t;
     if (t < CK && l < K) {
         const uint32_t c = (uint32_t) t;
-        // ring offset of row c; column-contiguous data sits XOR-swizzled by (c mod W) elements (see saso_tile_kernel)
-        const uint32_t base = c * SASO_ROWB | (cols_contig ? (c & (uint32_t)(32 / HALVES - 1)) * (4u * HALVES) : 0u);
+        const uint32_t base = c * pitch_el;
         fy_vector<KMAX>(ctr, key, co + l, vec_nnz, dim_major, [&](int j, int64_t idx, bool negative) {
             const int64_t r = idx - ro;
             if (r >= 0 && r < M) {
@@ -218,6 +219,37 @@ template <> __device__ __forceinline__ float lds_signed<float>(uint32_t addr, ui
                  : "=f"(v) : "r"(addr), "r"(code));
     return v;
 }
+// elements first .. n-1 of a slot whose codes sit in shared memory at code_addr, code_addr + step_bytes, ...:
+// acc += (+/-) A value. A warp-uniform loop (bra.uni: no reconvergence bookkeeping).
+template <typename T> __device__ __forceinline__ void slot_tail(T& acc, uint32_t code_addr, int first, int n, uint32_t lanebase, int step_bytes);
+template <> __device__ __forceinline__ void slot_tail<double>(double& acc, uint32_t code_addr, int first, int n, uint32_t lanebase, int step_bytes) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 i, ca, code, a, lo, hi;\n\t.reg .f64 v;\n\t"
+                 "setp.le.s32 p, %3, %2;\n\t@p bra.uni TAIL_DONE;\n\t"
+                 "mov.b32 i, %2;\n\tmov.b32 ca, %1;\n"
+                 "TAIL_LOOP:\n\t"
+                 "ld.shared.b32 code, [ca];\n\t"
+                 "shl.b32 a, code, 3;\n\tadd.u32 a, a, %4;\n\t"
+                 "ld.shared.v2.b32 {lo, hi}, [a];\n\t"
+                 "lop3.b32 hi, hi, code, 0x80000000, 0x78;\n\t"
+                 "mov.b64 v, {lo, hi};\n\tadd.f64 %0, %0, v;\n\t"
+                 "add.u32 ca, ca, %5;\n\tadd.s32 i, i, 1;\n\tsetp.lt.s32 p, i, %3;\n\t@p bra.uni TAIL_LOOP;\n"
+                 "TAIL_DONE:\n\t}"
+                 : "+d"(acc) : "r"(code_addr), "r"(first), "r"(n), "r"(lanebase), "r"(step_bytes));
+}
+template <> __device__ __forceinline__ void slot_tail<float>(float& acc, uint32_t code_addr, int first, int n, uint32_t lanebase, int step_bytes) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 i, ca, code, a, x;\n\t.reg .f32 v;\n\t"
+                 "setp.le.s32 p, %3, %2;\n\t@p bra.uni TAIL_DONE;\n\t"
+                 "mov.b32 i, %2;\n\tmov.b32 ca, %1;\n"
+                 "TAIL_LOOP:\n\t"
+                 "ld.shared.b32 code, [ca];\n\t"
+                 "shl.b32 a, code, 2;\n\tadd.u32 a, a, %4;\n\t"
+                 "ld.shared.b32 x, [a];\n\t"
+                 "lop3.b32 x, x, code, 0x80000000, 0x78;\n\t"
+                 "mov.b32 v, x;\n\tadd.f32 %0, %0, v;\n\t"
+                 "add.u32 ca, ca, %5;\n\tadd.s32 i, i, 1;\n\tsetp.lt.s32 p, i, %3;\n\t@p bra.uni TAIL_LOOP;\n"
+                 "TAIL_DONE:\n\t}"
+                 : "+f"(acc) : "r"(code_addr), "r"(first), "r"(n), "r"(lanebase), "r"(step_bytes));
+}
 // volatile: keeps the code loads where they are written (one slot ahead of their use) instead of all up front
 __device__ __forceinline__ uint32_t ld_code(const uint32_t* p, bool in_smem) {
     uint32_t v;
@@ -229,9 +261,11 @@ __device__ __forceinline__ uint32_t ld_code(const uint32_t* p, bool in_smem) {
 constexpr int SASO_NU = 3;          // elements of a slot handled by predicated straight-line code; the rest loop
 
 // slots [0, NS) of this warp: acc[s] += sum of the gathered (signed) A values of its elements.
-// codes: this lane's first code (step = codes per element); abase: shared address of the stage's A chunk.
+// codes: this lane's first code (step = codes per element); lanebase: shared address of this lane's column in row 0 of
+// the stage's A chunk. Address of an element = lanebase + (code << log2(sizeof(T))); the shift drops the sign bit.
 template <typename T, int NS, bool IN_SMEM>
-__device__ __forceinline__ void saso_consume(T (&acc)[NS], const uint32_t* codes, int step, uint32_t abase, uint32_t lx, const uint16_t* cnts) {
+__device__ __forceinline__ void saso_consume(T (&acc)[NS], const uint32_t* codes, int step, uint32_t lanebase, const uint16_t* cnts) {
+    constexpr int SH = sizeof(T) == 8 ? 3 : 2;
     uint32_t c[SASO_NU];
 #pragma unroll
     for (int i = 0; i < SASO_NU; ++i) c[i] = ld_code(codes + i * step, IN_SMEM);
@@ -244,18 +278,20 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], const uint32_t* codes
             const int n = (int)((cw[e >> 1] >> (16 * (e & 1))) & 0xffffu);
             uint32_t addr[SASO_NU], cc[SASO_NU];
 #pragma unroll
-            for (int i = 0; i < SASO_NU; ++i) { cc[i] = c[i]; addr[i] = abase + ((c[i] & SASO_AMASK) ^ lx); }
+            for (int i = 0; i < SASO_NU; ++i) { cc[i] = c[i]; addr[i] = lanebase + (c[i] << SH); }
             const uint32_t* cur = codes;
             codes += n * step;
 #pragma unroll
             for (int i = 0; i < SASO_NU; ++i) c[i] = ld_code(codes + i * step, IN_SMEM);       // next slot's codes
 #pragma unroll
             for (int i = 0; i < SASO_NU; ++i) gather_add_if<T>(acc[g + e], addr[i], cc[i], n, i);
-            if (n > SASO_NU) {
+            if (IN_SMEM) {
+                slot_tail<T>(acc[g + e], smem_u32(cur + SASO_NU * step), SASO_NU, n, lanebase, step * 4);
+            } else if (n > SASO_NU) {
 #pragma unroll 1
                 for (int i = SASO_NU; i < n; ++i) {
-                    const uint32_t code = ld_code(cur + i * step, IN_SMEM);
-                    acc[g + e] += lds_signed<T>(abase + ((code & SASO_AMASK) ^ lx), code);
+                    const uint32_t code = ld_code(cur + i * step, false);
+                    acc[g + e] += lds_signed<T>(lanebase + (code << SH), code);
                 }
             }
         }
@@ -263,9 +299,10 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], const uint32_t* codes
 }
 
 // COLS_CONTIG: columns of the data view are contiguous (sx_l == 1); otherwise rows are (sx_j == 1).
-// Ring layout of one A chunk: row c is 128 bytes at offset c * 128. Row-contiguous data is copied as is (16-byte
-// cp.async); column-contiguous data is copied element by element (8 / 4-byte cp.async, lanes run down a column) to
-// position jj ^ (c mod W) of row c, which spreads both that transposing write and the gather over all banks.
+// Ring layout of one A chunk: row c is 128 bytes at offset c * pitch. Row-contiguous data is copied as is (16-byte
+// cp.async, pitch 128); column-contiguous data is copied element by element (8 / 4-byte cp.async, lanes run down a
+// column) with a pitch of 128 bytes + one element, which spreads that transposing write over all banks while the gather
+// (lanes along a row) stays contiguous.
 template <typename T, bool COLS_CONTIG>
 __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoArgs<T> a) {
     constexpr int W = SASO_ROWB / (int) sizeof(T);     // columns per CTA: 16 doubles / 32 floats
@@ -276,8 +313,10 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t smem0 = smem_u32(smem);
     const int CK = a.CK;
-    const int a_bytes = CK * SASO_ROWB;
-    const int stage_bytes = a_bytes + SASO_ROWB + CNT_BYTES + a.cap * HALVES * 4;   // A | zero row | counts | codes
+    constexpr int PITCH = SASO_ROWB + (COLS_CONTIG ? (int) sizeof(T) : 0);
+    const int a_bytes = CK * PITCH;
+    const int az_bytes = (a_bytes + PITCH + 15) & ~15;                               // A chunk + its zero row
+    const int stage_bytes = az_bytes + CNT_BYTES + a.cap * HALVES * 4;               // A | zero row | counts | codes
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int sub = lane / W, jl = lane % W;
@@ -295,8 +334,8 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     const int bucket = b_first + warp;                 // warp owns rows [bucket*64, bucket*64+64) of the window
     const bool active = bucket < a.nbuckets;
 
-    if (tid < SASO_NST * (SASO_ROWB / 16))             // the zero rows of the stages
-        *reinterpret_cast<uint4*>(smem + (size_t)(tid / (SASO_ROWB / 16)) * stage_bytes + a_bytes + (tid % (SASO_ROWB / 16)) * 16) = make_uint4(0, 0, 0, 0);
+    if (tid < SASO_NST * (SASO_ROWB / 8))              // the zero rows of the stages
+        *reinterpret_cast<uint2*>(smem + (size_t)(tid / (SASO_ROWB / 8)) * stage_bytes + a_bytes + (tid % (SASO_ROWB / 8)) * 8) = make_uint2(0, 0);
 
     // A chunk, slot counts and codes of chunk ch -> stage s; [lo, hi) = the row block's range of the code stream
     auto load_async = [&](int ch, int s, uint32_t lo, uint32_t hi) {
@@ -313,20 +352,20 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
         } else if (tid < CK) {
             const int64_t l = (int64_t) ch * CK + tid;
             const T* src = a.X + (l < a.K ? l : 0) + j0 * a.sx_j;
-            const uint32_t row = st + tid * SASO_ROWB;
+            const uint32_t row = st + tid * PITCH;
 #pragma unroll 8
             for (int jj = 0; jj < W; ++jj) {
                 const uint32_t nb = (l < a.K && j0 + jj < a.N) ? (uint32_t) sizeof(T) : 0u;
-                cp_async_small<(int) sizeof(T)>(row + ((jj ^ (tid & (W - 1))) * (int) sizeof(T)), nb ? src + jj * a.sx_j : a.X, nb);
+                cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), nb ? src + jj * a.sx_j : a.X, nb);
             }
         }
         const uint8_t* csrc = reinterpret_cast<const uint8_t*>(a.cnt + (size_t) ch * a.cnt_stride + (size_t) rb * SASO_WARPS * NS);
-        if (tid < CNT_BYTES / 16) cp_async16(st + a_bytes + SASO_ROWB + tid * 16, csrc + tid * 16, 16);
+        if (tid < CNT_BYTES / 16) cp_async16(st + az_bytes + tid * 16, csrc + tid * 16, 16);
         uint32_t nel = hi + SASO_PAD - lo;
         nel = nel > (uint32_t) a.cap ? (uint32_t) a.cap : nel;
         const int npiece = (int)((nel * HALVES * 4 + 15) / 16);
         const uint8_t* ssrc = reinterpret_cast<const uint8_t*>(a.stream + (size_t) ch * a.stream_stride + (size_t) lo * HALVES);
-        const uint32_t sdst = st + a_bytes + SASO_ROWB + CNT_BYTES;
+        const uint32_t sdst = st + az_bytes + CNT_BYTES;
         for (int p = tid; p < npiece; p += SASO_THREADS) cp_async16(sdst + p * 16, ssrc + p * 16, 16);
     };
     auto ws_at = [&](int ch, int b) -> uint32_t { return ch < ce ? __ldg(a.ws + (size_t) ch * a.ws_stride + b) : 0u; };
@@ -359,14 +398,14 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
         if (active && a.dbg_skip != 1) {
             const uint32_t st = smem0 + (uint32_t)(it % SASO_NST) * stage_bytes;
             const uint8_t* st8 = smem + (size_t)(it % SASO_NST) * stage_bytes;
-            const uint16_t* cnts = reinterpret_cast<const uint16_t*>(st8 + a_bytes + SASO_ROWB) + warp * NS;
+            const uint16_t* cnts = reinterpret_cast<const uint16_t*>(st8 + az_bytes) + warp * NS;
             if (end + SASO_PAD - lo <= (uint32_t) a.cap) {
-                const uint32_t* codes = reinterpret_cast<const uint32_t*>(st8 + a_bytes + SASO_ROWB + CNT_BYTES) + (size_t)(first - lo) * HALVES + sub;
-                saso_consume<T, NS, true>(acc, codes, HALVES, st, lx, cnts);
+                const uint32_t* codes = reinterpret_cast<const uint32_t*>(st8 + az_bytes + CNT_BYTES) + (size_t)(first - lo) * HALVES + sub;
+                saso_consume<T, NS, true>(acc, codes, HALVES, st + lx, cnts);
             } else {
                 // the stage could not hold this warp's codes (far tail of the distribution): read them from global memory
                 const uint32_t* codes = a.stream + (size_t) ch * a.stream_stride + (size_t) first * HALVES + sub;
-                saso_consume<T, NS, false>(acc, codes, HALVES, st, lx, cnts);
+                saso_consume<T, NS, false>(acc, codes, HALVES, st + lx, cnts);
             }
         }
     }
@@ -428,7 +467,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     for (int ck = 512; ck >= 64; ck -= 64) {
         const double ent_rb = (double) ck * (double) vec_nnz * (double)(M < SASO_R ? M : SASO_R) / (double) S_rows;
         const int c = (((int)(HALVES == 2 ? ent_rb : 1.25 * ent_rb) + 64) + 31) & ~31;
-        const size_t sb = (size_t) ck * SASO_ROWB + SASO_ROWB + SASO_WARPS * NS * 2 + (size_t) c * HALVES * 4;
+        const size_t pitch = SASO_ROWB + (cols_contig ? sizeof(T) : 0);
+        const size_t sb = (((size_t) ck * pitch + pitch + 15) & ~(size_t) 15) + SASO_WARPS * NS * 2 + (size_t) c * HALVES * 4;
         if (SASO_NST * sb <= SMEM_MAX && (int64_t) ck <= ((K + 63) & ~(int64_t) 63)) { CK = ck; cap = c; stage = sb; break; }
     }
     if (CK == 0) return RBX_ERR_UNSUPPORTED;
