@@ -28,6 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 D, VEC_NNZ, KEY = 2048, 8, 1997
 M_FULL, N_COLS = 1 << 20, 2048
+REF_ROWS = 1 << 17          # rows of A per step of the `--impl reference` arm (1/8 of the workload, ~0.5 s of CPU work)
 
 
 def flops(m, n):
@@ -91,10 +92,9 @@ def cpu_reference_leg(threads_note=True, budget_rows=None):
         kind, lib = "reference", ol.REF
     else:
         kind, lib = "port", None
-    m = budget_rows or (1 << 15)
+    m = budget_rows or (1 << 18)
     n = N_COLS
-    rng = np.random.default_rng(99)
-    A = rng.standard_normal(m * n)
+    A = _cpu_sample(np, m, n)
     B = np.zeros(D * n)
     t0 = time.perf_counter()
     rc = ol.sketch_sparseop("f64", "L", "C", "N", "N", D, n, m, 1.0, D, m, VEC_NNZ, "S", [0, 0, 0, 0], [KEY, 0], 0, 0, A, m, 0.0, B, D,
@@ -107,6 +107,17 @@ def cpu_reference_leg(threads_note=True, budget_rows=None):
                       f"fill_sparse + lskges timed together, OpenMP threads={cores}"}
 
 
+_SAMPLE = {}
+
+
+def _cpu_sample(np, m, n):
+    """synthetic Gaussian rows of A for the CPU legs (generated once per process, not timed)"""
+    if (m, n) not in _SAMPLE:
+        _SAMPLE.clear()
+        _SAMPLE[(m, n)] = np.random.default_rng(99).standard_normal(m * n)
+    return _SAMPLE[(m, n)]
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -114,7 +125,7 @@ def run_reference(args):
     vals = []
     leg = None
     for i in range(args.warmup + args.steps):
-        leg = cpu_reference_leg(budget_rows=1 << 14)
+        leg = cpu_reference_leg(budget_rows=REF_ROWS)
         if i >= args.warmup:
             vals.append(leg)
     v = statistics.mean(x["value"] for x in vals)
@@ -122,8 +133,8 @@ def run_reference(args):
     leg["value"] = v
     line = {"impl": "reference", "metric": "sketch_gflops", "value": v, "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": {"workload": "C2: SASO SparseSkOp<double> vec_nnz=8 d=2048, left sketch of dense A (lskges); CPU sample m=16384 rows x 2048 cols",
-                                             "d": D, "n": N_COLS, "m_sample": 1 << 14, "vec_nnz": VEC_NNZ},
+            "data": "synthetic", "config": {"workload": "C2: SASO SparseSkOp<double> vec_nnz=8 d=2048, left sketch of dense A (lskges); CPU sample m=%d rows x 2048 cols per step" % REF_ROWS,
+                                             "d": D, "n": N_COLS, "m_sample": REF_ROWS, "vec_nnz": VEC_NNZ},
             "cpu_baseline": {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": v, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -206,8 +217,15 @@ def main():
     alg_bytes = 8.0 * m * n + 8.0 * D * n
     k_ms = statistics.mean(per_step)
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes": alg_bytes}
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "saso_traffic.json")
+    if os.path.exists(tp) and m == M_FULL:
+        tj = json.load(open(tp)).get("ColMajor" if lay == "C" else "RowMajor")
+        if tj:
+            traffic, traffic_src = tj["dram_bytes"], tj["source"]
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
+                "traffic_source": traffic_src, "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes": alg_bytes,
+                "kernel": "saso_tile_kernel<double> (+ saso_prep_kernel and saso_reduce_kernel, < 1% of the step, inside the same events)"}
 
     # end to end through the host-pointer C ABI (rank-local; N>1: every rank stages its own slab concurrently)
     e2e = None

@@ -323,11 +323,15 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     // the row blocks of one (column segment, split) are adjacent block ids: they run together and share A through L2
     const int rb = blockIdx.x % a.nrb;
     const int cid = blockIdx.x / a.nrb;
-    const int jb = cid % a.njb;
-    const int ms = cid / a.njb;
+    // Row-contiguous data: neighbouring CTAs take neighbouring column segments of the same rows, and a split owns a
+    // contiguous range of chunks. Column-contiguous data: every column is its own set of pages, so the splits of one
+    // column segment run side by side on interleaved chunks and walk the same pages together (TLB reach).
+    const int jb = COLS_CONTIG ? cid / a.msplit : cid % a.njb;
+    const int ms = COLS_CONTIG ? cid % a.msplit : cid / a.njb;
     const int per = (a.nchunks + a.msplit - 1) / a.msplit;
-    const int cb = ms * per;
-    const int ce = (cb + per < a.nchunks) ? cb + per : a.nchunks;
+    const int cstep = COLS_CONTIG ? a.msplit : 1;
+    const int cb = COLS_CONTIG ? ms : ms * per;
+    const int ce = COLS_CONTIG ? a.nchunks : ((cb + per < a.nchunks) ? cb + per : a.nchunks);
     const int64_t j0 = (int64_t) jb * W;
     const int b_first = rb * SASO_WARPS;
     const int b_last = (b_first + SASO_WARPS < a.nbuckets) ? b_first + SASO_WARPS : a.nbuckets;
@@ -338,25 +342,41 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
         *reinterpret_cast<uint2*>(smem + (size_t)(tid / (SASO_ROWB / 8)) * stage_bytes + a_bytes + (tid % (SASO_ROWB / 8)) * 8) = make_uint2(0, 0);
 
     // A chunk, slot counts and codes of chunk ch -> stage s; [lo, hi) = the row block's range of the code stream
+    // tiles that touch neither edge of A take the copy loops without per-piece bounds arithmetic
+    const bool cols_inside = j0 + W <= a.N;
     auto load_async = [&](int ch, int s, uint32_t lo, uint32_t hi) {
         const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
+        const bool inside = cols_inside && (int64_t)(ch + 1) * CK <= a.K;
         if (!COLS_CONTIG) {
-            for (int p = tid; p < CK * 8; p += SASO_THREADS) {
-                const int row = p >> 3, q = p & 7;
-                const int64_t l = (int64_t) ch * CK + row, col = j0 + (int64_t) q * EP;
-                int64_t nb = (l < a.K) ? (a.N - col) * (int64_t) sizeof(T) : 0;
-                nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
-                const T* src = nb > 0 ? a.X + l * a.sx_l + col : a.X;
-                cp_async16(st + p * 16, src, (uint32_t) nb);
+            if (inside) {
+                const T* src = a.X + ((int64_t) ch * CK + (tid >> 3)) * a.sx_l + j0 + (tid & 7) * EP;
+                const int64_t step = (int64_t)(SASO_THREADS / 8) * a.sx_l;
+                uint32_t dst = st + tid * 16;
+                for (int i = 0; i < CK / (SASO_THREADS / 8); ++i) { cp_async16(dst, src, 16); dst += SASO_THREADS * 16; src += step; }
+            } else {
+                for (int p = tid; p < CK * 8; p += SASO_THREADS) {
+                    const int row = p >> 3, q = p & 7;
+                    const int64_t l = (int64_t) ch * CK + row, col = j0 + (int64_t) q * EP;
+                    int64_t nb = (l < a.K) ? (a.N - col) * (int64_t) sizeof(T) : 0;
+                    nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+                    const T* src = nb > 0 ? a.X + l * a.sx_l + col : a.X;
+                    cp_async16(st + p * 16, src, (uint32_t) nb);
+                }
             }
         } else if (tid < CK) {
             const int64_t l = (int64_t) ch * CK + tid;
-            const T* src = a.X + (l < a.K ? l : 0) + j0 * a.sx_j;
             const uint32_t row = st + tid * PITCH;
-#pragma unroll 8
-            for (int jj = 0; jj < W; ++jj) {
-                const uint32_t nb = (l < a.K && j0 + jj < a.N) ? (uint32_t) sizeof(T) : 0u;
-                cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), nb ? src + jj * a.sx_j : a.X, nb);
+            if (inside) {
+                const T* src = a.X + l + j0 * a.sx_j;
+#pragma unroll
+                for (int jj = 0; jj < W; ++jj) { cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), src, (uint32_t) sizeof(T)); src += a.sx_j; }
+            } else {
+                const T* src = a.X + (l < a.K ? l : 0) + j0 * a.sx_j;
+#pragma unroll 4
+                for (int jj = 0; jj < W; ++jj) {
+                    const uint32_t nb = (l < a.K && j0 + jj < a.N) ? (uint32_t) sizeof(T) : 0u;
+                    cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), nb ? src + jj * a.sx_j : a.X, nb);
+                }
             }
         }
         const uint8_t* csrc = reinterpret_cast<const uint8_t*>(a.cnt + (size_t) ch * a.cnt_stride + (size_t) rb * SASO_WARPS * NS);
@@ -372,11 +392,11 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
 
     constexpr int DIST = SASO_NST - 1;                 // prefetch distance in chunks
     for (int s = 0; s < DIST; ++s) {
-        if (cb + s < ce) load_async(cb + s, s, ws_at(cb + s, b_first), ws_at(cb + s, b_last));
+        if (cb + s * cstep < ce) load_async(cb + s * cstep, s, ws_at(cb + s * cstep, b_first), ws_at(cb + s * cstep, b_last));
         cp_async_commit();
     }
     // stream positions, fetched one iteration ahead of their use
-    uint32_t pf_lo = ws_at(cb + DIST, b_first), pf_hi = ws_at(cb + DIST, b_last);            // for the next prefetch
+    uint32_t pf_lo = ws_at(cb + DIST * cstep, b_first), pf_hi = ws_at(cb + DIST * cstep, b_last);            // for the next prefetch
     uint32_t my_lo = ws_at(cb, b_first), my_first = 0, my_end = 0;                             // for the chunk being consumed
     if (active) { my_first = ws_at(cb, bucket); my_end = ws_at(cb, bucket + 1); }
 
@@ -385,16 +405,16 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     for (int s = 0; s < NS; ++s) acc[s] = (T) 0;
     const uint32_t lx = (uint32_t) jl * (uint32_t) sizeof(T);
 
-    for (int ch = cb, it = 0; ch < ce; ++ch, ++it) {
+    for (int ch = cb, it = 0; ch < ce; ch += cstep, ++it) {
         cp_async_wait<DIST - 1>();
         __syncthreads();                                // chunk `it` has landed; everyone is done with chunk it-1
-        const int nxt = ch + DIST;
+        const int nxt = ch + DIST * cstep;
         if (nxt < ce) load_async(nxt, (it + DIST) % SASO_NST, pf_lo, pf_hi);
         cp_async_commit();
-        pf_lo = ws_at(nxt + 1, b_first); pf_hi = ws_at(nxt + 1, b_last);
+        pf_lo = ws_at(nxt + cstep, b_first); pf_hi = ws_at(nxt + cstep, b_last);
         const uint32_t lo = my_lo, first = my_first, end = my_end;
-        my_lo = ws_at(ch + 1, b_first);
-        if (active) { my_first = ws_at(ch + 1, bucket); my_end = ws_at(ch + 1, bucket + 1); }
+        my_lo = ws_at(ch + cstep, b_first);
+        if (active) { my_first = ws_at(ch + cstep, bucket); my_end = ws_at(ch + cstep, bucket + 1); }
         if (active && a.dbg_skip != 1) {
             const uint32_t st = smem0 + (uint32_t)(it % SASO_NST) * stage_bytes;
             const uint8_t* st8 = smem + (size_t)(it % SASO_NST) * stage_bytes;
