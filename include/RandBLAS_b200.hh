@@ -1,0 +1,611 @@
+// RandBLAS_b200.hh -- the RandBLAS C++ surface for the sketching hot path, implemented on the rbx C ABI (include/rbx.h).
+//
+// A caller of RandBLAS (https://github.com/BallisticLA/RandBLAS) that uses the types and functions below can include
+// this header instead of <RandBLAS.hh> and link librbx.so: same namespaces, names, template parameters, argument order
+// and precondition failures (RandBLAS::Error, like RandBLAS::exceptions::Error). Bodies marshal plain data to the
+// extern "C" entry points; no CUDA header is needed to compile a caller (g++ is enough).
+//
+// Reference interfaces mirrored (paths under the RandBLAS tree):
+//   RNGState                      base.hh:161-232          MajorAxis                 base.hh:138-150
+//   DenseDist / DenseSkOp         dense_skops.hh:204-419   fill_dense x3             dense_skops.hh:486-592
+//   SparseDist / SparseSkOp       sparse_skops.hh:134-377  fill_sparse               sparse_skops.hh:389-413
+//   COOMatrix/CSRMatrix/CSCMatrix sparse_data/*.hh         sketch_general x4         skge.hh:771-1214
+//   sketch_vector x2              skve.hh:152-258          sketch_symmetric x4       sksy.hh:165-537
+//   sketch_sparse x2              sksp.hh:464-616
+//
+// Memory: by default pointers are HOST pointers, exactly like the reference; the call stages through HBM
+// (rbx_host_* entry points). Define RBX_DEVICE_POINTERS before including this header (or set
+// RandBLAS::device_pointers() = true at run time) when A, B and operator buffers already live in device memory.
+// Only RNG = r123::Philox4x32 (the reference's default) is supported.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <vector>
+#include <algorithm>
+#include <cmath>
+#include "rbx.h"
+
+#ifndef BLAS_HH      // BLAS++'s enums, when BLAS++ itself is not on the include path
+namespace blas {
+enum class Layout : char { ColMajor = 'C', RowMajor = 'R' };
+enum class Op : char { NoTrans = 'N', Trans = 'T', ConjTrans = 'C' };
+enum class Uplo : char { Upper = 'U', Lower = 'L', General = 'G' };
+enum class Side : char { Left = 'L', Right = 'R' };
+}
+#endif
+
+namespace r123 { struct Philox4x32 {}; }
+
+namespace RandBLAS {
+
+class Error : public std::runtime_error {
+public:
+    explicit Error(const std::string& what) : std::runtime_error(what) {}
+};
+namespace exceptions { using Error = ::RandBLAS::Error; }
+
+#define randblas_require(cond) do { if (!(cond)) throw ::RandBLAS::Error(std::string("(" #cond ") was required, but did not hold, in function ") + __func__); } while (0)
+
+inline bool& device_pointers() {
+#ifdef RBX_DEVICE_POINTERS
+    static bool v = true;
+#else
+    static bool v = false;
+#endif
+    return v;
+}
+// stream used by the device-pointer entry points of the calling thread (a cudaStream_t; nullptr = default stream)
+inline void*& current_stream() { static thread_local void* s = nullptr; return s; }
+
+namespace detail {
+inline void check(int rc, const char* where) {
+    if (rc == RBX_OK) return;
+    if (rc == RBX_ERR_ARG) throw Error(std::string("a precondition of ") + where + " was required, but did not hold");
+    throw std::runtime_error(std::string(where) + ": " + rbx_strerror(rc));
+}
+inline char ch(blas::Layout l) { return l == blas::Layout::ColMajor ? 'C' : 'R'; }
+inline char ch(blas::Op o) { return o == blas::Op::NoTrans ? 'N' : 'T'; }
+template <typename T> struct is_real : std::integral_constant<bool, std::is_same<T, float>::value || std::is_same<T, double>::value> {};
+
+// RAII device buffer for the host-pointer paths that have no single C entry point
+struct DevBuf {
+    void* p = nullptr;
+    DevBuf() = default;
+    DevBuf(const void* host, uint64_t bytes) { upload(host, bytes); }
+    void alloc(uint64_t bytes) { check(rbx_malloc(&p, bytes), "rbx_malloc"); }
+    void upload(const void* host, uint64_t bytes) { alloc(bytes); if (host) check(rbx_memcpy_h2d(p, host, bytes, nullptr), "rbx_memcpy_h2d"); }
+    ~DevBuf() { rbx_free(p); }
+    DevBuf(const DevBuf&) = delete; DevBuf& operator=(const DevBuf&) = delete;
+};
+}  // namespace detail
+
+// ---------------------------------------------------------------------------------------------------
+// base.hh
+// ---------------------------------------------------------------------------------------------------
+enum class MajorAxis : char { Short = 'S', Long = 'L', Undefined = 'U' };
+
+template <typename RNG = r123::Philox4x32>
+struct RNGState {
+    static_assert(std::is_same<RNG, r123::Philox4x32>::value, "only r123::Philox4x32 is implemented on the device");
+    using generator = RNG;
+    uint32_t counter[4];
+    uint32_t key[2];
+    RNGState() : counter{0, 0, 0, 0}, key{0, 0} {}
+    RNGState(uint32_t k) : counter{0, 0, 0, 0}, key{k, 0} {}           // base.hh:205
+    // base.hh:217-232: plain copies
+};
+
+inline int64_t safe_int_product(int64_t a, int64_t b) {                 // base.hh:121-135
+    if (a != 0 && b != 0) {
+        const int64_t c = (int64_t)((uint64_t) a * (uint64_t) b);
+        if (c / a != b) throw std::overflow_error("overflow in integer product");
+        return c;
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// dense_skops.hh
+// ---------------------------------------------------------------------------------------------------
+enum class DenseDistName : char { Gaussian = 'G', Uniform = 'U', BlackBox = 'B' };
+
+struct DenseDist {
+    const int64_t n_rows;
+    const int64_t n_cols;
+    const DenseDistName family;
+    const MajorAxis major_axis;
+    DenseDist(int64_t n_rows, int64_t n_cols, DenseDistName dn = DenseDistName::Gaussian, MajorAxis ma = MajorAxis::Long)
+        : n_rows(n_rows), n_cols(n_cols), family(dn), major_axis(ma) {}
+};
+
+inline blas::Layout dist_to_layout(const DenseDist& D) {                 // dense_skops.hh:297-310
+    randblas_require(D.major_axis != MajorAxis::Undefined);
+    return rbx_dist_to_layout(D.n_rows, D.n_cols, (char) D.major_axis) == 'C' ? blas::Layout::ColMajor : blas::Layout::RowMajor;
+}
+inline int64_t major_axis_length(const DenseDist& D) {                   // dense_skops.hh:312-316
+    randblas_require(D.major_axis != MajorAxis::Undefined);
+    return rbx_major_axis_length(D.n_rows, D.n_cols, (char) D.major_axis);
+}
+template <typename T> inline T isometry_scale_factor(DenseDist D) { return std::pow((T) std::min(D.n_rows, D.n_cols), (T) -0.5); }
+
+namespace dense {
+template <typename RNG>
+inline RNGState<RNG> compute_next_state(DenseDist D, RNGState<RNG> state) {   // dense_skops.hh:172-191
+    if (D.major_axis == MajorAxis::Undefined) return state;
+    RNGState<RNG> out = state;
+    rbx_dense_next_state(D.n_rows, D.n_cols, (char) D.major_axis, state.counter, out.counter);
+    return out;
+}
+}  // namespace dense
+
+template <typename T, typename RNG = r123::Philox4x32>
+struct DenseSkOp {
+    using generator = RNG;
+    using state_type = RNGState<RNG>;
+    using buffer_type = T;
+    const DenseDist dist;
+    const RNGState<RNG> seed_state;
+    const RNGState<RNG> next_state;
+    T* buff = nullptr;                         // host memory (or device memory when device_pointers())
+    blas::Layout layout;
+    bool del_buff_on_destruct = false;
+    const int64_t n_rows, n_cols;
+
+    DenseSkOp(DenseDist dist, RNGState<RNG> const& state, T* buff = nullptr)
+        : dist(dist), seed_state(state), next_state(dense::compute_next_state(dist, state)), buff(buff),
+          layout(dist_to_layout(dist)), n_rows(dist.n_rows), n_cols(dist.n_cols) {}
+    DenseSkOp(DenseDist dist, uint32_t key, T* buff = nullptr) : DenseSkOp(dist, RNGState<RNG>(key), buff) {}
+    DenseSkOp(DenseDist dist, RNGState<RNG> const& seed, RNGState<RNG> const& next, T* buff, blas::Layout layout, bool del)
+        : dist(dist), seed_state(seed), next_state(next), buff(buff), layout(layout), del_buff_on_destruct(del),
+          n_rows(dist.n_rows), n_cols(dist.n_cols) {}
+    ~DenseSkOp() {
+        if (del_buff_on_destruct && buff) { if (device_pointers()) rbx_free(buff); else delete[] buff; }
+    }
+    DenseSkOp(const DenseSkOp&) = delete;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// sparse_skops.hh
+// ---------------------------------------------------------------------------------------------------
+struct SparseDist {
+    const int64_t n_rows;
+    const int64_t n_cols;
+    const int64_t vec_nnz;
+    const MajorAxis major_axis = MajorAxis::Short;
+};
+
+namespace sparse {
+template <typename RNG>
+inline RNGState<RNG> compute_next_state(SparseDist D, RNGState<RNG> state) {  // sparse_skops.hh:115-126
+    RNGState<RNG> out = state;
+    rbx_sparse_next_state(D.n_rows, D.n_cols, D.vec_nnz, (char) D.major_axis, state.counter, out.counter);
+    return out;
+}
+}  // namespace sparse
+
+template <typename T, typename RNG = r123::Philox4x32, typename sint_t = int64_t>
+struct SparseSkOp {
+    static_assert(std::is_same<sint_t, int64_t>::value || std::is_same<sint_t, int32_t>::value, "sint_t must be int64_t or int");
+    using generator = RNG;
+    using state_type = RNGState<RNG>;
+    using index_t = sint_t;
+    using scalar_t = T;
+    const SparseDist dist;
+    const RNGState<RNG> seed_state;
+    const RNGState<RNG> next_state;
+    const bool own_memory = true;
+    bool known_filled = false;
+    sint_t* rows = nullptr;
+    sint_t* cols = nullptr;
+    T* vals = nullptr;
+    const int64_t n_rows, n_cols;
+
+    SparseSkOp(SparseDist dist, const RNGState<RNG>& state)              // sparse_skops.hh:261-279
+        : dist(dist), seed_state(state), next_state(sparse::compute_next_state(dist, state)), n_rows(dist.n_rows), n_cols(dist.n_cols) {
+        const int64_t minor = (dist.major_axis == MajorAxis::Short) ? std::max(dist.n_rows, dist.n_cols) : std::min(dist.n_rows, dist.n_cols);
+        const int64_t nnz = dist.vec_nnz * minor;
+        randblas_require(!device_pointers());        // owning constructor allocates host memory, as the reference does
+        rows = new sint_t[nnz]; cols = new sint_t[nnz]; vals = new T[nnz];
+    }
+    SparseSkOp(SparseDist dist, uint32_t key) : SparseSkOp(dist, RNGState<RNG>(key)) {}
+    SparseSkOp(SparseDist dist, const RNGState<RNG>& state, sint_t* rows, sint_t* cols, T* vals)   // :315-334 (view)
+        : dist(dist), seed_state(state), next_state(sparse::compute_next_state(dist, state)), own_memory(false),
+          rows(rows), cols(cols), vals(vals), n_rows(dist.n_rows), n_cols(dist.n_cols) {}
+    ~SparseSkOp() { if (own_memory) { delete[] rows; delete[] cols; delete[] vals; } }
+    SparseSkOp(const SparseSkOp&) = delete;
+};
+
+template <typename SKOP>
+inline int64_t nnz(const SKOP& S) {                                       // sparse_skops.hh:465-472
+    const bool saso = S.dist.major_axis == MajorAxis::Short;
+    const int64_t minor = saso ? std::max(S.dist.n_rows, S.dist.n_cols) : std::min(S.dist.n_rows, S.dist.n_cols);
+    return S.dist.vec_nnz * minor;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// sparse_data/{coo,csr,csc}_matrix.hh -- own-or-view containers (index_base Zero only)
+// ---------------------------------------------------------------------------------------------------
+namespace sparse_data {
+enum class IndexBase : char { Zero = 'Z', One = 'O' };
+
+template <typename T, typename sint_t = int64_t>
+struct COOMatrix {
+    using scalar_t = T; using index_t = sint_t;
+    const int64_t n_rows, n_cols; const bool own_memory; int64_t nnz = 0; const IndexBase index_base = IndexBase::Zero;
+    T* vals = nullptr; sint_t* rows = nullptr; sint_t* cols = nullptr;
+    COOMatrix(int64_t n_rows, int64_t n_cols) : n_rows(n_rows), n_cols(n_cols), own_memory(true) {}
+    COOMatrix(int64_t n_rows, int64_t n_cols, int64_t nnz, T* vals, sint_t* rows, sint_t* cols)
+        : n_rows(n_rows), n_cols(n_cols), own_memory(false), nnz(nnz), vals(vals), rows(rows), cols(cols) {}
+    void reserve(int64_t n) { randblas_require(own_memory && vals == nullptr); nnz = n; vals = new T[n]; rows = new sint_t[n]; cols = new sint_t[n]; }
+    ~COOMatrix() { if (own_memory) { delete[] vals; delete[] rows; delete[] cols; } }
+    COOMatrix(const COOMatrix&) = delete;
+};
+template <typename T, typename sint_t = int64_t>
+struct CSRMatrix {
+    using scalar_t = T; using index_t = sint_t;
+    const int64_t n_rows, n_cols; const bool own_memory; int64_t nnz = 0; const IndexBase index_base = IndexBase::Zero;
+    T* vals = nullptr; sint_t* rowptr = nullptr; sint_t* colidxs = nullptr;
+    CSRMatrix(int64_t n_rows, int64_t n_cols) : n_rows(n_rows), n_cols(n_cols), own_memory(true) {}
+    CSRMatrix(int64_t n_rows, int64_t n_cols, int64_t nnz, T* vals, sint_t* rowptr, sint_t* colidxs)
+        : n_rows(n_rows), n_cols(n_cols), own_memory(false), nnz(nnz), vals(vals), rowptr(rowptr), colidxs(colidxs) {}
+    void reserve(int64_t n) { randblas_require(own_memory && vals == nullptr); nnz = n; vals = new T[n]; rowptr = new sint_t[n_rows + 1]; colidxs = new sint_t[n]; }
+    ~CSRMatrix() { if (own_memory) { delete[] vals; delete[] rowptr; delete[] colidxs; } }
+    CSRMatrix(const CSRMatrix&) = delete;
+};
+template <typename T, typename sint_t = int64_t>
+struct CSCMatrix {
+    using scalar_t = T; using index_t = sint_t;
+    const int64_t n_rows, n_cols; const bool own_memory; int64_t nnz = 0; const IndexBase index_base = IndexBase::Zero;
+    T* vals = nullptr; sint_t* rowidxs = nullptr; sint_t* colptr = nullptr;
+    CSCMatrix(int64_t n_rows, int64_t n_cols) : n_rows(n_rows), n_cols(n_cols), own_memory(true) {}
+    CSCMatrix(int64_t n_rows, int64_t n_cols, int64_t nnz, T* vals, sint_t* rowidxs, sint_t* colptr)
+        : n_rows(n_rows), n_cols(n_cols), own_memory(false), nnz(nnz), vals(vals), rowidxs(rowidxs), colptr(colptr) {}
+    void reserve(int64_t n) { randblas_require(own_memory && vals == nullptr); nnz = n; vals = new T[n]; rowidxs = new sint_t[n]; colptr = new sint_t[n_cols + 1]; }
+    ~CSCMatrix() { if (own_memory) { delete[] vals; delete[] rowidxs; delete[] colptr; } }
+    CSCMatrix(const CSCMatrix&) = delete;
+};
+}  // namespace sparse_data
+using sparse_data::COOMatrix; using sparse_data::CSRMatrix; using sparse_data::CSCMatrix;
+
+namespace detail {
+// elements spanned by a rows x cols matrix with leading dimension ld
+inline uint64_t span(blas::Layout l, int64_t rows, int64_t cols, int64_t ld) {
+    if (rows <= 0 || cols <= 0) return 0;
+    return l == blas::Layout::ColMajor ? (uint64_t) ld * (cols - 1) + rows : (uint64_t) ld * (rows - 1) + cols;
+}
+template <typename sint_t>
+inline std::vector<int64_t> widen(const sint_t* p, int64_t n) { return std::vector<int64_t>(p, p + n); }
+
+#define RBX_PICK(T, name) (std::is_same<T, float>::value ? (void*) name##_f32 : (void*) name##_f64)
+template <typename T> struct fn {
+    using fill_dense_t = int (*)(char, int64_t, int64_t, char, char, int64_t, int64_t, int64_t, int64_t, T*, const uint32_t*, const uint32_t*, uint32_t*, void*);
+    using host_fill_dense_t = int (*)(char, int64_t, int64_t, char, char, int64_t, int64_t, int64_t, int64_t, T*, const uint32_t*, const uint32_t*, uint32_t*);
+    using sketch_dense_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                                   const T*, char, int64_t, int64_t, const T*, int64_t, T, T*, int64_t, void*);
+    using host_sketch_dense_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                                        int64_t, int64_t, const T*, int64_t, T, T*, int64_t);
+    using sketch_sparseop_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, int64_t, char, const uint32_t*, const uint32_t*,
+                                      int64_t, int64_t, const T*, int64_t, T, T*, int64_t, void*);
+    using host_sketch_sparseop_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, int64_t, char, const uint32_t*, const uint32_t*,
+                                           int64_t, int64_t, const T*, int64_t, T, T*, int64_t);
+    using spmm_coo_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, int64_t, const int64_t*, const int64_t*, const T*,
+                               int64_t, int64_t, const T*, int64_t, T, T*, int64_t, void*);
+    using sparsedata_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                                 int64_t, int64_t, char, int64_t, int64_t, int64_t, const T*, const int64_t*, const int64_t*, int64_t, int64_t, T, T*, int64_t, void*);
+    static fill_dense_t fill_dense() { return (fill_dense_t) RBX_PICK(T, rbx_fill_dense); }
+    static host_fill_dense_t host_fill_dense() { return (host_fill_dense_t) RBX_PICK(T, rbx_host_fill_dense); }
+    static sketch_dense_t sketch_dense() { return (sketch_dense_t) RBX_PICK(T, rbx_sketch_dense); }
+    static host_sketch_dense_t host_sketch_dense() { return (host_sketch_dense_t) RBX_PICK(T, rbx_host_sketch_dense); }
+    static sketch_sparseop_t sketch_sparseop() { return (sketch_sparseop_t) RBX_PICK(T, rbx_sketch_sparseop); }
+    static host_sketch_sparseop_t host_sketch_sparseop() { return (host_sketch_sparseop_t) RBX_PICK(T, rbx_host_sketch_sparseop); }
+    static spmm_coo_t spmm_coo() { return (spmm_coo_t) RBX_PICK(T, rbx_spmm_coo); }
+    static sparsedata_t sparsedata() { return (sparsedata_t) RBX_PICK(T, rbx_sketch_sparsedata); }
+};
+#undef RBX_PICK
+}  // namespace detail
+
+// ---------------------------------------------------------------------------------------------------
+// fill_dense (dense_skops.hh:486-592) and fill_sparse (sparse_skops.hh:389-413)
+// ---------------------------------------------------------------------------------------------------
+template <typename T, typename RNG = r123::Philox4x32>
+inline RNGState<RNG> fill_dense(blas::Layout layout, const DenseDist& D, int64_t n_rows, int64_t n_cols, int64_t ro_s, int64_t co_s,
+                                T* buff, const RNGState<RNG>& seed) {
+    static_assert(detail::is_real<T>::value, "T must be float or double");
+    if (D.family == DenseDistName::BlackBox) throw std::invalid_argument("fill_dense cannot be called with the BlackBox distribution.");
+    RNGState<RNG> next = seed;
+    const int rc = device_pointers()
+        ? detail::fn<T>::fill_dense()(detail::ch(layout), D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis, n_rows, n_cols, ro_s, co_s,
+                                      buff, seed.counter, seed.key, next.counter, current_stream())
+        : detail::fn<T>::host_fill_dense()(detail::ch(layout), D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis, n_rows, n_cols, ro_s, co_s,
+                                           buff, seed.counter, seed.key, next.counter);
+    detail::check(rc, "fill_dense");
+    return next;
+}
+template <typename T, typename RNG = r123::Philox4x32>
+inline RNGState<RNG> fill_dense(const DenseDist& D, T* buff, const RNGState<RNG>& seed) {
+    return fill_dense(dist_to_layout(D), D, D.n_rows, D.n_cols, 0, 0, buff, seed);
+}
+template <typename DenseSkOpT>
+inline void fill_dense(DenseSkOpT& S) {
+    using T = typename DenseSkOpT::buffer_type;
+    randblas_require(S.buff == nullptr);
+    const uint64_t n = (uint64_t) S.dist.n_rows * S.dist.n_cols;
+    if (device_pointers()) { void* p = nullptr; detail::check(rbx_malloc(&p, n * sizeof(T)), "rbx_malloc"); S.buff = (T*) p; }
+    else S.buff = new T[n];
+    S.del_buff_on_destruct = true;
+    fill_dense(S.dist, S.buff, S.seed_state);
+}
+
+template <typename SparseSkOpT>
+inline void fill_sparse(SparseSkOpT& S) {
+    using T = typename SparseSkOpT::scalar_t; using I = typename SparseSkOpT::index_t;
+    const int64_t n = nnz(S);
+    uint32_t next[4];
+    auto call = [&](I* r, I* c, T* v) -> int {
+        if constexpr (std::is_same<T, float>::value && std::is_same<I, int32_t>::value)
+            return rbx_fill_sparse_f32_i32(S.dist.n_rows, S.dist.n_cols, S.dist.vec_nnz, (char) S.dist.major_axis, S.seed_state.counter, S.seed_state.key, r, c, v, next, current_stream());
+        else if constexpr (std::is_same<T, float>::value)
+            return rbx_fill_sparse_f32_i64(S.dist.n_rows, S.dist.n_cols, S.dist.vec_nnz, (char) S.dist.major_axis, S.seed_state.counter, S.seed_state.key, r, c, v, next, current_stream());
+        else if constexpr (std::is_same<I, int32_t>::value)
+            return rbx_fill_sparse_f64_i32(S.dist.n_rows, S.dist.n_cols, S.dist.vec_nnz, (char) S.dist.major_axis, S.seed_state.counter, S.seed_state.key, r, c, v, next, current_stream());
+        else
+            return rbx_fill_sparse_f64_i64(S.dist.n_rows, S.dist.n_cols, S.dist.vec_nnz, (char) S.dist.major_axis, S.seed_state.counter, S.seed_state.key, r, c, v, next, current_stream());
+    };
+    if (device_pointers()) {
+        detail::check(call(S.rows, S.cols, S.vals), "fill_sparse");
+    } else {
+        detail::DevBuf r, c, v;
+        r.alloc(n * sizeof(I)); c.alloc(n * sizeof(I)); v.alloc(n * sizeof(T));
+        detail::check(call((I*) r.p, (I*) c.p, (T*) v.p), "fill_sparse");
+        detail::check(rbx_memcpy_d2h(S.rows, r.p, n * sizeof(I), nullptr), "rbx_memcpy_d2h");
+        detail::check(rbx_memcpy_d2h(S.cols, c.p, n * sizeof(I), nullptr), "rbx_memcpy_d2h");
+        detail::check(rbx_memcpy_d2h(S.vals, v.p, n * sizeof(T), nullptr), "rbx_memcpy_d2h");
+        detail::check(rbx_stream_synchronize(nullptr), "rbx_stream_synchronize");
+    }
+    S.known_filled = true;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// cores: dense::lskge3 / rskge3 (skge.hh:173-215, 320-364), sparse::lskges / rskges (skge.hh:485-510, 616-641)
+// side 'L': dims (d, n, m); side 'R': dims (m, d, n)   -- see rbx.h
+// ---------------------------------------------------------------------------------------------------
+namespace detail {
+inline void ab_dims(char side, blas::Op opA, int64_t p0, int64_t p1, int64_t p2, int64_t& rA, int64_t& cA, int64_t& rB, int64_t& cB) {
+    if (side == 'L') { rA = (opA == blas::Op::NoTrans) ? p2 : p1; cA = (opA == blas::Op::NoTrans) ? p1 : p2; rB = p0; cB = p1; }
+    else             { rA = (opA == blas::Op::NoTrans) ? p0 : p2; cA = (opA == blas::Op::NoTrans) ? p2 : p0; rB = p0; cB = p1; }
+}
+
+template <typename T, typename RNG>
+inline void sk3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                DenseSkOp<T, RNG>& S, int64_t ro_s, int64_t co_s, const T* A, int64_t lda, T beta, T* B, int64_t ldb) {
+    const DenseDist& D = S.dist;
+    if (device_pointers()) {
+        check(fn<T>::sketch_dense()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
+                                    S.seed_state.counter, S.seed_state.key, S.buff, ch(S.layout), ro_s, co_s, A, lda, beta, B, ldb, current_stream()),
+              "sketch_general");
+    } else if (S.buff == nullptr) {
+        check(fn<T>::host_sketch_dense()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
+                                         S.seed_state.counter, S.seed_state.key, ro_s, co_s, A, lda, beta, B, ldb),
+              "sketch_general");
+    } else {
+        // explicit host operator (DenseSkOp::buff, possibly BlackBox): validate first (null data pointers => dry run is not
+        // available here, so let the device call validate), staging S, A and B by hand
+        int64_t rA, cA, rB, cB; ab_dims(side, opA, p0, p1, p2, rA, cA, rB, cB);
+        randblas_require(lda >= (layout == blas::Layout::ColMajor ? rA : cA));
+        randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
+        const uint64_t nA = span(layout, rA, cA, lda), nB = span(layout, rB, cB, ldb);
+        DevBuf dS(S.buff, (uint64_t) D.n_rows * D.n_cols * sizeof(T)), dA(A, nA * sizeof(T)), dB(beta != (T) 0 ? B : nullptr, nB * sizeof(T));
+        check(fn<T>::sketch_dense()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
+                                    S.seed_state.counter, S.seed_state.key, (const T*) dS.p, ch(S.layout), ro_s, co_s, (const T*) dA.p, lda, beta,
+                                    (T*) dB.p, ldb, nullptr), "sketch_general");
+        check(rbx_memcpy_d2h(B, dB.p, nB * sizeof(T), nullptr), "rbx_memcpy_d2h");
+        check(rbx_stream_synchronize(nullptr), "rbx_stream_synchronize");
+    }
+}
+
+template <typename T, typename RNG, typename sint_t>
+inline void sk3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                SparseSkOp<T, RNG, sint_t>& S, int64_t ro_s, int64_t co_s, const T* A, int64_t lda, T beta, T* B, int64_t ldb) {
+    const SparseDist& D = S.dist;
+    if (!S.known_filled) {
+        // the reference fills the operator here (skge.hh:503-504); on the device it is regenerated inside the sketch
+        const int rc = device_pointers()
+            ? fn<T>::sketch_sparseop()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, D.vec_nnz, (char) D.major_axis,
+                                       S.seed_state.counter, S.seed_state.key, ro_s, co_s, A, lda, beta, B, ldb, current_stream())
+            : fn<T>::host_sketch_sparseop()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, D.vec_nnz, (char) D.major_axis,
+                                            S.seed_state.counter, S.seed_state.key, ro_s, co_s, A, lda, beta, B, ldb);
+        check(rc, "sketch_general");
+        return;
+    }
+    // explicit triplets (the caller may have edited them): COO spmm, spmm_dispatch.hh:48-200
+    const int64_t n = nnz(S);
+    if (device_pointers()) {
+        if constexpr (std::is_same<sint_t, int64_t>::value) {
+            check(fn<T>::spmm_coo()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, n, S.rows, S.cols, S.vals,
+                                    ro_s, co_s, A, lda, beta, B, ldb, current_stream()), "sketch_general");
+        } else {
+            throw std::runtime_error("explicit 32-bit COO operators need 64-bit indices on the device; use an unfilled SparseSkOp");
+        }
+        return;
+    }
+    int64_t rA, cA, rB, cB; ab_dims(side, opA, p0, p1, p2, rA, cA, rB, cB);
+    randblas_require(lda >= (layout == blas::Layout::ColMajor ? rA : cA));
+    randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
+    const uint64_t nA = span(layout, rA, cA, lda), nB = span(layout, rB, cB, ldb);
+    const std::vector<int64_t> r64 = widen(S.rows, n), c64 = widen(S.cols, n);
+    DevBuf dr(r64.data(), n * 8), dc(c64.data(), n * 8), dv(S.vals, n * sizeof(T)), dA(A, nA * sizeof(T)), dB(beta != (T) 0 ? B : nullptr, nB * sizeof(T));
+    check(fn<T>::spmm_coo()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, n, (const int64_t*) dr.p, (const int64_t*) dc.p,
+                            (const T*) dv.p, ro_s, co_s, (const T*) dA.p, lda, beta, (T*) dB.p, ldb, nullptr), "sketch_general");
+    check(rbx_memcpy_d2h(B, dB.p, nB * sizeof(T), nullptr), "rbx_memcpy_d2h");
+    check(rbx_stream_synchronize(nullptr), "rbx_stream_synchronize");
+}
+}  // namespace detail
+
+namespace dense {
+template <typename T, typename SKOP>
+inline void lskge3(blas::Layout layout, blas::Op opS, blas::Op opA, int64_t d, int64_t n, int64_t m, T alpha, SKOP& S, int64_t ro_s, int64_t co_s,
+                   const T* A, int64_t lda, T beta, T* B, int64_t ldb) { detail::sk3('L', layout, opS, opA, d, n, m, alpha, S, ro_s, co_s, A, lda, beta, B, ldb); }
+template <typename T, typename SKOP>
+inline void rskge3(blas::Layout layout, blas::Op opA, blas::Op opS, int64_t m, int64_t d, int64_t n, T alpha, const T* A, int64_t lda, SKOP& S,
+                   int64_t ro_s, int64_t co_s, T beta, T* B, int64_t ldb) { detail::sk3('R', layout, opS, opA, m, d, n, alpha, S, ro_s, co_s, A, lda, beta, B, ldb); }
+}  // namespace dense
+namespace sparse {
+template <typename T, typename SKOP>
+inline void lskges(blas::Layout layout, blas::Op opS, blas::Op opA, int64_t d, int64_t n, int64_t m, T alpha, SKOP& S, int64_t ro_s, int64_t co_s,
+                   const T* A, int64_t lda, T beta, T* B, int64_t ldb) { detail::sk3('L', layout, opS, opA, d, n, m, alpha, S, ro_s, co_s, A, lda, beta, B, ldb); }
+template <typename T, typename SKOP>
+inline void rskges(blas::Layout layout, blas::Op opA, blas::Op opS, int64_t m, int64_t d, int64_t n, T alpha, const T* A, int64_t lda, SKOP& S,
+                   int64_t ro_s, int64_t co_s, T beta, T* B, int64_t ldb) { detail::sk3('R', layout, opS, opA, m, d, n, alpha, S, ro_s, co_s, A, lda, beta, B, ldb); }
+}  // namespace sparse
+
+// ---------------------------------------------------------------------------------------------------
+// sketch_general (skge.hh:771-1214): left / right, with and without sub-matrix offsets; SKOP = DenseSkOp or SparseSkOp
+// ---------------------------------------------------------------------------------------------------
+template <typename T, typename SKOP>
+inline void sketch_general(blas::Layout layout, blas::Op opS, blas::Op opA, int64_t d, int64_t n, int64_t m, T alpha, SKOP& S, int64_t ro_s,
+                           int64_t co_s, const T* A, int64_t lda, T beta, T* B, int64_t ldb) {
+    detail::sk3('L', layout, opS, opA, d, n, m, alpha, S, ro_s, co_s, A, lda, beta, B, ldb);
+}
+template <typename T, typename SKOP>
+inline void sketch_general(blas::Layout layout, blas::Op opA, blas::Op opS, int64_t m, int64_t d, int64_t n, T alpha, const T* A, int64_t lda,
+                           SKOP& S, int64_t ro_s, int64_t co_s, T beta, T* B, int64_t ldb) {
+    detail::sk3('R', layout, opS, opA, m, d, n, alpha, S, ro_s, co_s, A, lda, beta, B, ldb);
+}
+template <typename T, typename SKOP>
+inline void sketch_general(blas::Layout layout, blas::Op opS, blas::Op opA, int64_t d, int64_t n, int64_t m, T alpha, SKOP& S, const T* A,
+                           int64_t lda, T beta, T* B, int64_t ldb) {
+    if (opS == blas::Op::NoTrans) { randblas_require(S.dist.n_rows == d); randblas_require(S.dist.n_cols == m); }
+    else                          { randblas_require(S.dist.n_rows == m); randblas_require(S.dist.n_cols == d); }      // skge.hh:1104-1111
+    sketch_general(layout, opS, opA, d, n, m, alpha, S, (int64_t) 0, (int64_t) 0, A, lda, beta, B, ldb);
+}
+template <typename T, typename SKOP>
+inline void sketch_general(blas::Layout layout, blas::Op opA, blas::Op opS, int64_t m, int64_t d, int64_t n, T alpha, const T* A, int64_t lda,
+                           SKOP& S, T beta, T* B, int64_t ldb) {
+    if (opS == blas::Op::NoTrans) { randblas_require(S.dist.n_rows == n); randblas_require(S.dist.n_cols == d); }
+    else                          { randblas_require(S.dist.n_rows == d); randblas_require(S.dist.n_cols == n); }      // skge.hh:1206-1213
+    sketch_general(layout, opA, opS, m, d, n, alpha, A, lda, S, (int64_t) 0, (int64_t) 0, beta, B, ldb);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// sketch_vector (skve.hh:152-258)
+// ---------------------------------------------------------------------------------------------------
+template <typename T, typename SKOP>
+inline void sketch_vector(blas::Op opS, int64_t d, int64_t m, T alpha, SKOP& S, int64_t ro_s, int64_t co_s, const T* x, int64_t incx, T beta,
+                          T* y, int64_t incy) {
+    int64_t _d = d, _m = m;
+    if (opS == blas::Op::Trans) { _d = m; _m = d; }
+    sketch_general(blas::Layout::RowMajor, opS, blas::Op::NoTrans, _d, (int64_t) 1, _m, alpha, S, ro_s, co_s, x, incx, beta, y, incy);
+}
+template <typename T, typename SKOP>
+inline void sketch_vector(blas::Op opS, T alpha, SKOP& S, const T* x, int64_t incx, T beta, T* y, int64_t incy) {
+    sketch_vector(opS, S.dist.n_rows, S.dist.n_cols, alpha, S, (int64_t) 0, (int64_t) 0, x, incx, beta, y, incy);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// sketch_symmetric (sksy.hh:165-537); util::require_symmetric (util.hh:165-188) runs on the host copy of A
+// ---------------------------------------------------------------------------------------------------
+namespace util {
+template <typename T>
+inline void require_symmetric(blas::Layout layout, const T* A, int64_t n, int64_t lda, T tol) {
+    if (tol < 0) return;
+    std::vector<T> host;
+    if (device_pointers()) {                       // the check is O(n^2) host work in the reference; bring A over once
+        const uint64_t cnt = detail::span(layout, n, n, lda);
+        host.resize(cnt);
+        detail::check(rbx_memcpy_d2h(host.data(), A, cnt * sizeof(T), current_stream()), "rbx_memcpy_d2h");
+        detail::check(rbx_stream_synchronize(current_stream()), "rbx_stream_synchronize");
+        A = host.data();
+    }
+    const int64_t rs = layout == blas::Layout::ColMajor ? 1 : lda, cs = layout == blas::Layout::ColMajor ? lda : 1;
+    for (int64_t i = 0; i < n; ++i)
+        for (int64_t j = i + 1; j < n; ++j) {
+            const T Aij = A[i * rs + j * cs], Aji = A[j * rs + i * cs];
+            const T viol = std::abs(Aij - Aji), rel_tol = (std::abs(Aij) + std::abs(Aji) + 1) * tol;
+            if (viol > rel_tol) throw Error("Symmetry check failed, in function require_symmetric");
+        }
+}
+}  // namespace util
+
+template <typename T, typename SKOP>
+inline void sketch_symmetric(blas::Layout layout, int64_t n, int64_t d, T alpha, const T* A, int64_t lda, SKOP& S, int64_t ro_s, int64_t co_s,
+                             T beta, T* B, int64_t ldb, T sym_check_tol = 0) {
+    util::require_symmetric(layout, A, n, lda, sym_check_tol);
+    sketch_general(layout, blas::Op::NoTrans, blas::Op::NoTrans, n, d, n, alpha, A, lda, S, ro_s, co_s, beta, B, ldb);
+}
+template <typename T, typename SKOP>
+inline void sketch_symmetric(blas::Layout layout, int64_t d, int64_t n, T alpha, SKOP& S, int64_t ro_s, int64_t co_s, const T* A, int64_t lda,
+                             T beta, T* B, int64_t ldb, T sym_check_tol = 0) {
+    util::require_symmetric(layout, A, n, lda, sym_check_tol);
+    sketch_general(layout, blas::Op::NoTrans, blas::Op::NoTrans, d, n, n, alpha, S, ro_s, co_s, A, lda, beta, B, ldb);
+}
+template <typename T, typename SKOP>
+inline void sketch_symmetric(blas::Layout layout, T alpha, const T* A, int64_t lda, SKOP& S, T beta, T* B, int64_t ldb, T sym_check_tol = 0) {
+    const int64_t n = S.dist.n_rows, d = S.dist.n_cols;
+    util::require_symmetric(layout, A, n, lda, sym_check_tol);
+    sketch_general(layout, blas::Op::NoTrans, blas::Op::NoTrans, n, d, n, alpha, A, lda, S, (int64_t) 0, (int64_t) 0, beta, B, ldb);
+}
+template <typename T, typename SKOP>
+inline void sketch_symmetric(blas::Layout layout, T alpha, SKOP& S, const T* A, int64_t lda, T beta, T* B, int64_t ldb, T sym_check_tol = 0) {
+    const int64_t d = S.dist.n_rows, n = S.dist.n_cols;
+    util::require_symmetric(layout, A, n, lda, sym_check_tol);
+    sketch_general(layout, blas::Op::NoTrans, blas::Op::NoTrans, d, n, n, alpha, S, (int64_t) 0, (int64_t) 0, A, lda, beta, B, ldb);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// sketch_sparse (sksp.hh:464-616): dense operator applied to sparse data (COO / CSR / CSC)
+// ---------------------------------------------------------------------------------------------------
+namespace detail {
+template <typename T, typename I> inline void sp_arrays(const COOMatrix<T, I>& A, char& fmt, const I*& i0, int64_t& n0, const I*& i1, int64_t& n1) {
+    fmt = 'O'; i0 = A.rows; n0 = A.nnz; i1 = A.cols; n1 = A.nnz; }
+template <typename T, typename I> inline void sp_arrays(const CSRMatrix<T, I>& A, char& fmt, const I*& i0, int64_t& n0, const I*& i1, int64_t& n1) {
+    fmt = 'R'; i0 = A.rowptr; n0 = A.n_rows + 1; i1 = A.colidxs; n1 = A.nnz; }
+template <typename T, typename I> inline void sp_arrays(const CSCMatrix<T, I>& A, char& fmt, const I*& i0, int64_t& n0, const I*& i1, int64_t& n1) {
+    fmt = 'C'; i0 = A.rowidxs; n0 = A.nnz; i1 = A.colptr; n1 = A.n_cols + 1; }
+
+template <typename T, typename RNG, typename SpMat>
+inline void sksp3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, int64_t p0, int64_t p1, int64_t p2, T alpha, DenseSkOp<T, RNG>& S,
+                  int64_t ro_s, int64_t co_s, SpMat& A, int64_t ro_a, int64_t co_a, T beta, T* B, int64_t ldb) {
+    using I = typename SpMat::index_t;
+    randblas_require(A.index_base == sparse_data::IndexBase::Zero);           // spmm_dispatch.hh:89
+    randblas_require(S.buff == nullptr);                                       // the device path regenerates S from its seed
+    const DenseDist& D = S.dist;
+    char fmt; const I *i0, *i1; int64_t n0, n1;
+    sp_arrays(A, fmt, i0, n0, i1, n1);
+    if (device_pointers()) {
+        if constexpr (std::is_same<I, int64_t>::value) {
+            check(fn<T>::sparsedata()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
+                                      S.seed_state.counter, S.seed_state.key, ro_s, co_s, fmt, A.n_rows, A.n_cols, A.nnz, A.vals, i0, i1, ro_a, co_a,
+                                      beta, B, ldb, current_stream()), "sketch_sparse");
+        } else {
+            throw std::runtime_error("sketch_sparse on device pointers needs 64-bit indices");
+        }
+        return;
+    }
+    const int64_t rB = p0, cB = p1;
+    randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
+    const uint64_t nB = span(layout, rB, cB, ldb);
+    const std::vector<int64_t> a0 = widen(i0, n0), a1 = widen(i1, n1);
+    DevBuf d0(a0.data(), n0 * 8), d1(a1.data(), n1 * 8), dv(A.vals, A.nnz * sizeof(T)), dB(beta != (T) 0 ? B : nullptr, nB * sizeof(T));
+    check(fn<T>::sparsedata()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
+                              S.seed_state.counter, S.seed_state.key, ro_s, co_s, fmt, A.n_rows, A.n_cols, A.nnz, (const T*) dv.p,
+                              (const int64_t*) d0.p, (const int64_t*) d1.p, ro_a, co_a, beta, (T*) dB.p, ldb, nullptr), "sketch_sparse");
+    check(rbx_memcpy_d2h(B, dB.p, nB * sizeof(T), nullptr), "rbx_memcpy_d2h");
+    check(rbx_stream_synchronize(nullptr), "rbx_stream_synchronize");
+}
+}  // namespace detail
+
+template <typename T, typename RNG, typename SpMat>
+inline void sketch_sparse(blas::Layout layout, blas::Op opS, blas::Op opA, int64_t d, int64_t n, int64_t m, T alpha, DenseSkOp<T, RNG>& S,
+                          int64_t ro_s, int64_t co_s, SpMat& A, int64_t ro_a, int64_t co_a, T beta, T* B, int64_t ldb) {
+    detail::sksp3('L', layout, opS, opA, d, n, m, alpha, S, ro_s, co_s, A, ro_a, co_a, beta, B, ldb);
+}
+template <typename T, typename RNG, typename SpMat>
+inline void sketch_sparse(blas::Layout layout, blas::Op opA, blas::Op opS, int64_t m, int64_t d, int64_t n, T alpha, SpMat& A, int64_t ro_a,
+                          int64_t co_a, DenseSkOp<T, RNG>& S, int64_t ro_s, int64_t co_s, T beta, T* B, int64_t ldb) {
+    detail::sksp3('R', layout, opS, opA, m, d, n, alpha, S, ro_s, co_s, A, ro_a, co_a, beta, B, ldb);
+}
+
+}  // namespace RandBLAS

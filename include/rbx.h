@@ -35,6 +35,13 @@ int rbx_device_count(void);
 /* number of kernel launches issued by this library in this process so far (for bench accounting) */
 int64_t rbx_launch_count(void);
 
+/* ---- device memory for callers that do not link the CUDA runtime (the header layer in include/RandBLAS_b200.hh) ---- */
+int rbx_malloc(void** dev_ptr, uint64_t bytes);
+int rbx_free(void* dev_ptr);
+int rbx_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* stream);
+int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream);
+int rbx_stream_synchronize(void* stream);
+
 /* ---- RNG state algebra (host-side, exact) ------------------------------------------------------ */
 /* ctr += n with carry: Random123 array.h incr(); pinned by test/test_basic_rng/test_r123.cc:679-766 */
 void rbx_ctr_add(uint32_t ctr[4], uint64_t n);

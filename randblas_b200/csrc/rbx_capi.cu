@@ -526,6 +526,25 @@ RBX_DEF_SPARSE(f32_i64, float, int64_t)
 RBX_DEF_SPARSE(f64_i32, double, int32_t)
 RBX_DEF_SPARSE(f64_i64, double, int64_t)
 
+int rbx_malloc(void** dev_ptr, uint64_t bytes) {
+    if (!dev_ptr) return RBX_ERR_ARG;
+    *dev_ptr = nullptr;
+    RBX_NEED_DEVICE();
+    if (bytes == 0) return RBX_OK;
+    if (cudaMalloc(dev_ptr, (size_t) bytes) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    return RBX_OK;
+}
+int rbx_free(void* dev_ptr) { return (dev_ptr == nullptr || cudaFree(dev_ptr) == cudaSuccess) ? RBX_OK : RBX_ERR_CUDA; }
+int rbx_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* stream) {
+    if (bytes == 0) return RBX_OK;
+    return cudaMemcpyAsync(dst_dev, src_host, (size_t) bytes, cudaMemcpyHostToDevice, (cudaStream_t) stream) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;
+}
+int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream) {
+    if (bytes == 0) return RBX_OK;
+    return cudaMemcpyAsync(dst_host, src_dev, (size_t) bytes, cudaMemcpyDeviceToHost, (cudaStream_t) stream) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;
+}
+int rbx_stream_synchronize(void* stream) { return cudaStreamSynchronize((cudaStream_t) stream) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA; }
+
 int rbx_host_fill_sparse_f64_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
                                  int64_t* rows_host, int64_t* cols_host, double* vals_host, uint32_t next_ctr[4]) {
     return host_fill_sparse<double, int64_t>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, rows_host, cols_host, vals_host, next_ctr);

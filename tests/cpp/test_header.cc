@@ -1,0 +1,202 @@
+// Exercises include/RandBLAS_b200.hh the way a RandBLAS caller would (host pointers, the reference's argument order),
+// and checks every result against the CPU oracle (oracle/randblas_oracle.c -- test infrastructure, linked here only as
+// the checker). Built with g++ (no nvcc, no CUDA headers) by tests/test_cpp_header.py; runs on a GPU box.
+//
+// Mirrors the structure of the reference's own tests: test/test_datastructures/test_denseskop.cc (bit-exact fills,
+// next_state), test_sparseskop.cc (fill_sparse), test/test_matmul_cores/test_lskge3.cc, test_rskge3.cc, test_lskges.cc
+// (sketches against an explicit reference product within the comparison.hh bound).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <cmath>
+#include "RandBLAS_b200.hh"
+
+extern "C" {
+int orc_fill_dense_f32(char, int64_t, int64_t, char, char, int64_t, int64_t, int64_t, int64_t, float*, const uint32_t*, const uint32_t*, uint32_t*);
+int orc_fill_dense_f64(char, int64_t, int64_t, char, char, int64_t, int64_t, int64_t, int64_t, double*, const uint32_t*, const uint32_t*, uint32_t*);
+int orc_fill_sparse_f64_i64(int64_t, int64_t, int64_t, char, const uint32_t*, const uint32_t*, int64_t*, int64_t*, double*, uint32_t*);
+int orc_fill_sparse_f32_i32(int64_t, int64_t, int64_t, char, const uint32_t*, const uint32_t*, int32_t*, int32_t*, float*, uint32_t*);
+int orc_sketch_dense_f32(char, char, char, char, int64_t, int64_t, int64_t, float, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                         int64_t, int64_t, const float*, int64_t, float, float*, int64_t);
+int orc_sketch_dense_f64(char, char, char, char, int64_t, int64_t, int64_t, double, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                         int64_t, int64_t, const double*, int64_t, double, double*, int64_t);
+int orc_sketch_sparseop_f64(char, char, char, char, int64_t, int64_t, int64_t, double, int64_t, int64_t, int64_t, char, const uint32_t*, const uint32_t*,
+                            int64_t, int64_t, const double*, int64_t, double, double*, int64_t);
+int orc_sketch_sparsedata_f64(char, char, char, char, int64_t, int64_t, int64_t, double, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                              int64_t, int64_t, char, int64_t, int64_t, int64_t, const double*, const int64_t*, const int64_t*, int64_t, int64_t,
+                              double, double*, int64_t);
+}
+
+using namespace RandBLAS;
+static int failures = 0;
+#define CHECK(cond) do { if (!(cond)) { std::printf("FAIL %s:%d  %s\n", __FILE__, __LINE__, #cond); ++failures; } } while (0)
+
+template <typename T> static bool bits_equal(const std::vector<T>& a, const std::vector<T>& b) {
+    return a.size() == b.size() && std::memcmp(a.data(), b.data(), a.size() * sizeof(T)) == 0;
+}
+template <typename T> static double max_rel(const std::vector<T>& a, const std::vector<T>& b) {
+    double num = 0, den = 1e-300;
+    for (size_t i = 0; i < a.size(); ++i) { num = std::max(num, (double) std::abs(a[i] - b[i])); den = std::max(den, (double) std::abs(b[i])); }
+    return num / den;
+}
+
+static void test_fill_dense() {
+    for (auto fam : { DenseDistName::Gaussian, DenseDistName::Uniform })
+        for (auto ma : { MajorAxis::Long, MajorAxis::Short })
+            for (int64_t cols : { 10, 11, 12, 13 }) {            // all four n_cols % 4 phases
+                DenseDist D(7, cols, fam, ma);
+                RNGState<> seed(42);
+                std::vector<float> got(7 * cols), want(7 * cols);
+                RNGState<> next = fill_dense(D, got.data(), seed);
+                uint32_t nx[4];
+                CHECK(orc_fill_dense_f32(detail::ch(dist_to_layout(D)), 7, cols, (char) fam, (char) ma, 7, cols, 0, 0, want.data(), seed.counter, seed.key, nx) == 0);
+                CHECK(bits_equal(got, want));
+                CHECK(std::memcmp(next.counter, nx, 16) == 0);
+                DenseSkOp<float> S(D, seed);
+                CHECK(std::memcmp(S.next_state.counter, nx, 16) == 0);
+                // sub-matrix with offsets, both layouts, double
+                std::vector<double> g2(3 * 5), w2(3 * 5);
+                for (auto lay : { blas::Layout::ColMajor, blas::Layout::RowMajor }) {
+                    fill_dense(lay, D, 3, 5, 2, 4, g2.data(), seed);
+                    CHECK(orc_fill_dense_f64(detail::ch(lay), 7, cols, (char) fam, (char) ma, 3, 5, 2, 4, w2.data(), seed.counter, seed.key, nx) == 0);
+                    CHECK(bits_equal(g2, w2));
+                }
+            }
+    // fill_dense(DenseSkOp&) allocates, fills and owns the buffer
+    DenseSkOp<double> S(DenseDist(6, 40), 7);
+    fill_dense(S);
+    CHECK(S.buff != nullptr && S.del_buff_on_destruct);
+    std::vector<double> want(240), got(S.buff, S.buff + 240);
+    uint32_t nx[4];
+    orc_fill_dense_f64(detail::ch(S.layout), 6, 40, 'G', 'L', 6, 40, 0, 0, want.data(), S.seed_state.counter, S.seed_state.key, nx);
+    CHECK(bits_equal(got, want));
+    bool threw = false;
+    try { std::vector<float> b(4); fill_dense(DenseDist(2, 2, DenseDistName::BlackBox), b.data(), RNGState<>(0)); } catch (const std::invalid_argument&) { threw = true; }
+    CHECK(threw);
+}
+
+static void test_fill_sparse() {
+    for (auto ma : { MajorAxis::Short, MajorAxis::Long })
+        for (auto shape : { std::pair<int64_t, int64_t>{ 7, 20 }, { 20, 7 }, { 15, 15 } }) {
+            SparseDist D{ shape.first, shape.second, 3, ma };
+            SparseSkOp<double> S(D, 99);
+            fill_sparse(S);
+            const int64_t n = nnz(S);
+            std::vector<int64_t> r(n), c(n); std::vector<double> v(n); uint32_t nx[4];
+            CHECK(orc_fill_sparse_f64_i64(D.n_rows, D.n_cols, 3, (char) ma, S.seed_state.counter, S.seed_state.key, r.data(), c.data(), v.data(), nx) == 0);
+            CHECK(std::memcmp(r.data(), S.rows, n * 8) == 0 && std::memcmp(c.data(), S.cols, n * 8) == 0 && std::memcmp(v.data(), S.vals, n * 8) == 0);
+            CHECK(std::memcmp(nx, S.next_state.counter, 16) == 0);
+            SparseSkOp<float, r123::Philox4x32, int32_t> S32(D, 99);
+            fill_sparse(S32);
+            std::vector<int32_t> r32(n), c32(n); std::vector<float> v32(n);
+            CHECK(orc_fill_sparse_f32_i32(D.n_rows, D.n_cols, 3, (char) ma, S32.seed_state.counter, S32.seed_state.key, r32.data(), c32.data(), v32.data(), nx) == 0);
+            CHECK(std::memcmp(r32.data(), S32.rows, n * 4) == 0 && std::memcmp(c32.data(), S32.cols, n * 4) == 0 && std::memcmp(v32.data(), S32.vals, n * 4) == 0);
+        }
+}
+
+static std::vector<double> randmat(int64_t n, uint32_t key) {
+    std::vector<double> a(n);
+    fill_dense(DenseDist(n, 1), a.data(), RNGState<>(key));
+    return a;
+}
+
+static void test_sketch_dense() {
+    const int64_t d = 9, n = 13, m = 50;
+    DenseSkOp<double> S(DenseDist(d, m), 0);
+    std::vector<double> A = randmat(m * n, 99);
+    for (auto lay : { blas::Layout::ColMajor, blas::Layout::RowMajor }) {
+        const int64_t lda = lay == blas::Layout::ColMajor ? m : n, ldb = lay == blas::Layout::ColMajor ? d : n;
+        std::vector<double> B(d * n, 0.5), W(d * n, 0.5);
+        sketch_general(lay, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.5, S, A.data(), lda, -0.5, B.data(), ldb);
+        CHECK(orc_sketch_dense_f64('L', detail::ch(lay), 'N', 'N', d, n, m, 1.5, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, A.data(), lda, -0.5, W.data(), ldb) == 0);
+        CHECK(max_rel(B, W) < 1e-13);
+        // right sketch with the transposed operator: B (n x d) = A^T (n x m) * S^T (m x d)
+        const int64_t ldb2 = lay == blas::Layout::ColMajor ? n : d;
+        std::vector<double> B2(n * d, 0.0), W2(n * d, 0.0);
+        sketch_general(lay, blas::Op::Trans, blas::Op::Trans, n, d, m, 1.0, A.data(), lda, S, 0.0, B2.data(), ldb2);
+        CHECK(orc_sketch_dense_f64('R', detail::ch(lay), 'T', 'T', n, d, m, 1.0, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, A.data(), lda, 0.0, W2.data(), ldb2) == 0);
+        CHECK(max_rel(B2, W2) < 1e-13);
+    }
+    // explicit buffer == implicit operator
+    DenseSkOp<double> S2(DenseDist(d, m), 0);
+    fill_dense(S2);
+    std::vector<double> B(d * n, 0.0), W(d * n, 0.0);
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S2, A.data(), m, 0.0, B.data(), d);
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, A.data(), m, 0.0, W.data(), d);
+    CHECK(max_rel(B, W) < 1e-13);
+    // sketch_vector and dimension checks
+    std::vector<double> x = randmat(m, 5), y(d, 0.0), wy(d, 0.0);
+    sketch_vector(blas::Op::NoTrans, 1.0, S, x.data(), 1, 0.0, y.data(), 1);
+    orc_sketch_dense_f64('L', 'R', 'N', 'N', d, 1, m, 1.0, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, x.data(), 1, 0.0, wy.data(), 1);
+    CHECK(max_rel(y, wy) < 1e-13);
+    bool threw = false;
+    try { sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d + 1, n, m, 1.0, S, A.data(), m, 0.0, B.data(), d + 1); } catch (const Error&) { threw = true; }
+    CHECK(threw);
+    threw = false;
+    try { sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, 0, 0, A.data(), m - 1, 0.0, B.data(), d); } catch (const Error&) { threw = true; }
+    CHECK(threw);
+    // float
+    DenseSkOp<float> Sf(DenseDist(d, m, DenseDistName::Uniform), 3);
+    std::vector<float> Af(m * n), Bf(d * n, 0.f), Wf(d * n, 0.f);
+    fill_dense(DenseDist(m, n), Af.data(), RNGState<>(99));
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.f, Sf, Af.data(), m, 0.f, Bf.data(), d);
+    orc_sketch_dense_f32('L', 'C', 'N', 'N', d, n, m, 1.f, d, m, 'U', 'L', Sf.seed_state.counter, Sf.seed_state.key, 0, 0, Af.data(), m, 0.f, Wf.data(), d);
+    CHECK(max_rel(Bf, Wf) < 1e-5);
+}
+
+static void test_sketch_sparseop() {
+    const int64_t d = 64, n = 24, m = 700;
+    std::vector<double> A = randmat(m * n, 99);
+    for (auto lay : { blas::Layout::ColMajor, blas::Layout::RowMajor }) {
+        const int64_t lda = lay == blas::Layout::ColMajor ? m : n, ldb = lay == blas::Layout::ColMajor ? d : n;
+        SparseSkOp<double> S({ d, m, 8, MajorAxis::Short }, 1997);
+        std::vector<double> B(d * n, 0.0), W(d * n, 0.0), B2(d * n, 0.0);
+        sketch_general(lay, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, A.data(), lda, 0.0, B.data(), ldb);     // implicit (streaming kernel)
+        CHECK(orc_sketch_sparseop_f64('L', detail::ch(lay), 'N', 'N', d, n, m, 1.0, d, m, 8, 'S', S.seed_state.counter, S.seed_state.key, 0, 0, A.data(), lda, 0.0, W.data(), ldb) == 0);
+        CHECK(max_rel(B, W) < 1e-13);
+        fill_sparse(S);                                                                                                       // explicit triplets
+        sketch_general(lay, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, A.data(), lda, 0.0, B2.data(), ldb);
+        CHECK(max_rel(B2, W) < 1e-13);
+    }
+    // symmetric wrapper: A symmetric n x n, right sketch by an n x d LASO
+    const int64_t ns = 40, ds = 6;
+    std::vector<double> G = randmat(ns * ns, 3), Sym(ns * ns);
+    for (int64_t i = 0; i < ns; ++i) for (int64_t j = 0; j < ns; ++j) Sym[i + j * ns] = G[i + j * ns] + G[j + i * ns];
+    SparseSkOp<double> SL({ ns, ds, 2, MajorAxis::Long }, 5);
+    std::vector<double> B(ns * ds, 0.0), W(ns * ds, 0.0);
+    sketch_symmetric(blas::Layout::ColMajor, 1.0, Sym.data(), ns, SL, 0.0, B.data(), ns);
+    orc_sketch_sparseop_f64('R', 'C', 'N', 'N', ns, ds, ns, 1.0, ns, ds, 2, 'L', SL.seed_state.counter, SL.seed_state.key, 0, 0, Sym.data(), ns, 0.0, W.data(), ns);
+    CHECK(max_rel(B, W) < 1e-13);
+    Sym[1] += 1.0;
+    bool threw = false;
+    try { sketch_symmetric(blas::Layout::ColMajor, 1.0, Sym.data(), ns, SL, 0.0, B.data(), ns); } catch (const Error&) { threw = true; }
+    CHECK(threw);
+}
+
+static void test_sketch_sparse() {
+    // CSR data 30 x 20 with a few nonzeros per row, left sketch with a 5 x 30 Gaussian operator
+    const int64_t m = 30, n = 20, d = 5;
+    CSRMatrix<double> A(m, n);
+    A.reserve(3 * m);
+    std::vector<double> vals = randmat(3 * m, 8);
+    for (int64_t i = 0; i <= m; ++i) A.rowptr[i] = 3 * i;
+    for (int64_t i = 0; i < m; ++i) for (int k = 0; k < 3; ++k) { A.colidxs[3 * i + k] = (i * 7 + k * 5) % n; A.vals[3 * i + k] = vals[3 * i + k]; }
+    DenseSkOp<double> S(DenseDist(d, m), 0);
+    std::vector<double> B(d * n, 0.0), W(d * n, 0.0);
+    sketch_sparse(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, 0, 0, A, 0, 0, 0.0, B.data(), d);
+    CHECK(orc_sketch_sparsedata_f64('L', 'C', 'N', 'N', d, n, m, 1.0, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, 'R', m, n, A.nnz,
+                                    A.vals, A.rowptr, A.colidxs, 0, 0, 0.0, W.data(), d) == 0);
+    CHECK(max_rel(B, W) < 1e-13);
+}
+
+int main() {
+    if (rbx_device_count() < 1) { std::printf("no CUDA device: the product path has no CPU fallback\n"); return 77; }
+    test_fill_dense();
+    test_fill_sparse();
+    test_sketch_dense();
+    test_sketch_sparseop();
+    test_sketch_sparse();
+    std::printf(failures ? "FAILED (%d)\n" : "OK\n", failures);
+    return failures ? 1 : 0;
+}
