@@ -1,6 +1,344 @@
-// K2 tensor-core paths (placeholder dispatch until the tcgen05 / DMMA kernels land in this file).
+// K2 (tensor-core path, float): fused generate-and-contract GEMM on the 5th-generation tensor cores.
+//
+//   C (M x N) = alpha * Sop (M x K) * X (K x N) + beta * C,   Sop = a window of the implicit dense operator
+//
+// Replaces dense::lskge3 / rskge3 (skge.hh:173-215, 320-364) for large aligned float problems (BASELINE config 1):
+// the reference writes the d x m operator to memory and calls sgemm; here the operator tile goes from the Philox
+// counter straight into the shared-memory operand of tcgen05.mma and never exists in HBM.
+//
+//  * 128 x BN output tile per CTA (BN = 256: the FP32 accumulator is 128 lanes x 256 columns of TMEM), BK = 32 floats
+//    = one 128-byte swizzle atom per row; rings: 3 X tiles (TMA latency), 2 operator tiles and 2 X_lo tiles (224 KB).
+//  * FP32 accuracy from TF32 tensor cores: 3xTF32. Both operands are split x = hi + lo (hi = top 19 bits, lo = x - hi,
+//    exact in FP32) and D += hi*hi + lo*hi + hi*lo with FP32 accumulation in TMEM; the dropped lo*lo term is 2^-22
+//    relative, inside the reference's own GEMM tolerance (test/comparison.hh).
+//  * warp roles: warp 0 = TMA producer for X (cp.async.bulk.tensor, 128B swizzle), warp 1 = TMEM allocator + single
+//    MMA-issuing thread, warps 2..9 = generators: bit-exact Philox/Box-Muller (rbx_rng.cuh) -> hi/lo split -> swizzled
+//    K-major operand layout, then the hi/lo split of the X tile in place; they are also the epilogue warps
+//    (tcgen05.ld -> alpha/beta -> global, or split-K partials summed in a fixed order by a second kernel).
+//  * the CTAs of one row block (same operator rows, different columns of X) form a thread-block cluster of up to 4:
+//    each generates 1/CL of the operator tile and writes it into every peer's shared memory with st.async (remote
+//    store that completes bytes on the peer's mbarrier), so a Gaussian sample is generated once per cluster;
+//  * mbarriers: full_x (TMA -> generators), ready_s (st.async bytes from all peers -> MMA), ready_x (generators ->
+//    MMA), empty (tcgen05.commit multicast to the whole cluster -> TMA + generators), done (last commit -> epilogue).
+// Envelope: implicit operator whose parent rows run along the contraction axis (l_on_cols), window column offset a
+// multiple of 4, X with unit stride along the contraction axis (e.g. ColMajor A in a left sketch), 16-byte aligned.
+// Everything else returns RBX_ERR_UNSUPPORTED and takes the SIMT kernel.
+#include <cstdlib>
 #include "rbx_kernels.cuh"
+#include "rbx_tma.cuh"
+
 namespace rbx {
-int launch_sketch_dense_tc_f32(const GemmOperands<float>&, cudaStream_t) { return RBX_ERR_UNSUPPORTED; }
-int launch_sketch_dense_tc_f64(const GemmOperands<double>&, cudaStream_t) { return RBX_ERR_UNSUPPORTED; }
+
+constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32;
+constexpr int TC_XST = 3;           // raw / hi X tiles in flight (hides the TMA latency)
+constexpr int TC_LST = 2;           // operator (hi + lo) tiles and X_lo tiles (produced on chip, one stage ahead is enough)
+constexpr int TC_GEN_WARPS = 8, TC_THREADS = (2 + TC_GEN_WARPS) * 32;
+constexpr int TC_S_BYTES = TC_BM * TC_BK * 4;          // 16 KB: one of S_hi / S_lo
+constexpr int TC_X_BYTES = TC_BN * TC_BK * 4;          // 32 KB: one of X_hi / X_lo
+// shared-memory map: [X hi x3][X lo x2][S hi, S lo x2]
+constexpr int TC_OFF_XLO = TC_XST * TC_X_BYTES;
+constexpr int TC_OFF_S = TC_OFF_XLO + TC_LST * TC_X_BYTES;
+constexpr size_t TC_SMEM = (size_t) TC_OFF_S + TC_LST * 2 * TC_S_BYTES + 1024 /* alignment slack */;
+
+// ---- tcgen05 wrappers --------------------------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_commit_mcast(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta));
+    return r;
+}
+// 16-byte store into a (possibly remote) CTA's shared memory that completes 16 bytes on that CTA's mbarrier
+__device__ __forceinline__ void st_async_v4(uint32_t cluster_addr, float4 v, uint32_t cluster_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
+                 :: "r"(cluster_addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major operand tile, 128-byte rows, SWIZZLE_128B: 8-row groups are 1024 bytes apart (cute/arch/mma_sm100_desc.hpp fields)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);          // start address, bits [0,14)
+    d |= (uint64_t) 1 << 16;                               // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                      // stride byte offset, bits [32,46)
+    d |= (uint64_t) 1 << 46;                               // descriptor version (Blackwell)
+    d |= (uint64_t) 2 << 61;                               // layout type SWIZZLE_128B
+    return d;
+}
+// kind::tf32, FP32 accumulate, both operands K-major, M = 128, N = BN
+constexpr uint32_t tc_idesc(int bn) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+
+struct TcArgs {
+    DenseOpWindow w;
+    int64_t M, N, K;
+    float alpha, beta;
+    float* C; int64_t sc_i, sc_j;
+    float* partial;               // [ksplit][Npad][Mpad] when ksplit > 1
+    int64_t Mpad, Npad;
+    int nk, ksplit, tiles_n, dbg, cl;
+};
+
+template <char FAMILY>
+__global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_x[TC_XST], x_empty[TC_XST], ready_s[TC_LST], ready_x[TC_LST], l_empty[TC_LST], done;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ double tab[32];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    const uint32_t smem0 = smem_u32(smem);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    const int tile = blockIdx.x % (a.tiles_n * (int)((a.M + TC_BM - 1) / TC_BM));
+    const int ks = blockIdx.x / (a.tiles_n * (int)((a.M + TC_BM - 1) / TC_BM));
+    const int64_t i0 = (int64_t)(tile / a.tiles_n) * TC_BM, j0 = (int64_t)(tile % a.tiles_n) * TC_BN;
+    const int per = (a.nk + a.ksplit - 1) / a.ksplit;
+    const int kb = ks * per, ke = (kb + per < a.nk) ? kb + per : a.nk;
+    const int nit = ke - kb;
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_XST; ++s) { mbar_init(&full_x[s], 1); mbar_init(&x_empty[s], 1); }
+        for (int s = 0; s < TC_LST; ++s) { mbar_init(&ready_s[s], 1); mbar_init(&ready_x[s], TC_GEN_WARPS); mbar_init(&l_empty[s], (uint32_t) a.cl); }
+        mbar_init(&done, 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&tmap_x);
+    }
+    if (FAMILY == 'G') load_logf_tab(tab);
+    if (warp == 1) tmem_alloc(&tmem_base_s, TC_BN);
+    tc_fence_before();
+    __syncthreads();
+    if (a.cl > 1) cluster_sync_all();                      // peers' barriers are initialised before any remote traffic
+    tc_fence_after();
+    const uint32_t tmem_d = tmem_base_s;
+    const uint32_t crank = a.cl > 1 ? cluster_ctarank() : 0u;
+
+    if (warp == 0) {
+        // ---- TMA producer: raw X tile (BN rows of 32 floats) into the X_hi slot of the stage ----
+        if (lane == 0) {
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % TC_XST, u = it / TC_XST;
+                if (u > 0) mbar_wait(&x_empty[s], (u - 1) & 1);
+                if (a.dbg & 8) { mbar_arrive(&full_x[s]); continue; }
+                mbar_expect_tx(&full_x[s], TC_X_BYTES);
+                tma_load_2d(smem + (size_t) s * TC_X_BYTES, &tmap_x, (kb + it) * TC_BK, (int) j0, &full_x[s]);
+            }
+        }
+    } else if (warp == 1) {
+        // ---- MMA issuer ----
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc_idesc(TC_BN);
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
+                mbar_wait(&ready_s[s], u & 1);
+                mbar_wait(&ready_x[s], u & 1);
+                fence_proxy_async();                       // st.async / generic writes -> tensor-core (async proxy) reads
+                tc_fence_after();
+                const uint32_t sS = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES;
+                const uint64_t a_hi = umma_desc_sw128(sS), a_lo = umma_desc_sw128(sS + TC_S_BYTES);
+                const uint64_t b_hi = umma_desc_sw128(smem0 + (uint32_t) xs * TC_X_BYTES), b_lo = umma_desc_sw128(smem0 + TC_OFF_XLO + (uint32_t) s * TC_X_BYTES);
+#pragma unroll
+                for (int k = 0; k < ((a.dbg & 4) ? 0 : TC_BK / 8); ++k) {
+                    const uint64_t adv = (uint64_t)(k * 8 * 4 >> 4);          // 32 bytes per K step inside the swizzle atom
+                    umma_tf32(tmem_d, a_lo + adv, b_hi + adv, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    umma_tf32(tmem_d, a_hi + adv, b_lo + adv, idesc, 1u);
+                    umma_tf32(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                }
+                // when these MMAs have read their operands: the X slot is free for the TMA producer, the operator / X_lo slot
+                // is free in every CTA of the cluster (peers write operator rows into it)
+                umma_commit(&x_empty[xs]);
+                if (a.cl > 1) umma_commit_mcast(&l_empty[s], (uint16_t)((1u << a.cl) - 1u)); else umma_commit(&l_empty[s]);
+            }
+            umma_commit(&done);
+        }
+    } else {
+        // ---- generators / converters ----
+        const int gt = tid - 64;                           // 0 .. 255
+        const float scale = (FAMILY == 'U') ? (float) 1.7320508075688772 : 1.0f;
+        for (int it = 0; it < nit; ++it) {
+            const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
+            if (u > 0) mbar_wait(&l_empty[s], (u - 1) & 1);
+            const int64_t l0 = (int64_t)(kb + it) * TC_BK;
+            const int64_t cbase = (a.w.pc0 + l0) >> 2;     // first counter column of this K block (pc0 % 4 == 0)
+            if (gt == 0) mbar_expect_tx(&ready_s[s], 2 * TC_S_BYTES);      // hi + lo tiles, written by the whole cluster
+            const int rows_per = TC_BM / a.cl;                             // operator rows this CTA generates for the cluster
+            const uint32_t st_u32 = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES, bar_u32 = smem_u32(&ready_s[s]);
+            for (int e = gt; e < ((a.dbg & 1) ? 0 : rows_per * (TC_BK / 4)); e += TC_GEN_WARPS * 32) {
+                const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i0 + r < a.M && l0 + 4 * c < a.K) {
+                    const Ctr128 ctr = ctr_add(a.w.ctr, (uint64_t)((a.w.pr0 + i0 + r) * a.w.W + cbase + c));
+                    v = generate4<FAMILY>(philox4x32_10(ctr, a.w.key), tab);
+                    if (FAMILY == 'U') { v.x = __fmul_rn(v.x, scale); v.y = __fmul_rn(v.y, scale); v.z = __fmul_rn(v.z, scale); v.w = __fmul_rn(v.w, scale); }
+                    if (l0 + 4 * c + 1 >= a.K) v.y = 0.f;
+                    if (l0 + 4 * c + 2 >= a.K) v.z = 0.f;
+                    if (l0 + 4 * c + 3 >= a.K) v.w = 0.f;
+                }
+                float4 hi, lo;
+                hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
+                hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
+                hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
+                hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
+                const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+                for (int p = 0; p < a.cl; ++p) {
+                    const uint32_t dst = mapa_u32(st_u32 + off, (uint32_t) p), bar = mapa_u32(bar_u32, (uint32_t) p);
+                    st_async_v4(dst, hi, bar);
+                    st_async_v4(dst + TC_S_BYTES, lo, bar);
+                }
+            }
+            if ((a.dbg & 1) && gt == 0) {                  // debug: nothing generated, complete the bytes by hand
+                for (int p = 0; p < a.cl; ++p)
+                    asm volatile("mbarrier.complete_tx.relaxed.cluster.shared::cluster.b64 [%0], %1;" :: "r"(mapa_u32(bar_u32, (uint32_t) p)), "r"(2 * TC_S_BYTES / a.cl) : "memory");
+            }
+            mbar_wait(&full_x[xs], (it / TC_XST) & 1);
+            float4* xh = reinterpret_cast<float4*>(smem + (size_t) xs * TC_X_BYTES);
+            float4* xl = reinterpret_cast<float4*>(smem + TC_OFF_XLO + (size_t) s * TC_X_BYTES);
+#pragma unroll 4
+            for (int e = gt; e < ((a.dbg & 2) ? 0 : TC_X_BYTES / 16); e += TC_GEN_WARPS * 32) {
+                const float4 v = xh[e];
+                float4 hi, lo;
+                hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
+                hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
+                hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
+                hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
+                xh[e] = hi; xl[e] = lo;
+            }
+            fence_proxy_async();                           // generic-proxy writes -> visible to the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ready_x[s]);
+        }
+        // ---- epilogue: TMEM -> registers -> global ----
+        mbar_wait(&done, 0);
+        tc_fence_after();
+        const int lg = warp & 3;                           // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;                  // which half of the BN columns
+        const int64_t row = i0 + lg * 32 + lane;
+        for (int c0 = half * (TC_BN / 2); c0 < (half + 1) * (TC_BN / 2); c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t) c0, v);
+            if (row < a.M) {
+#pragma unroll
+                for (int q = 0; q < 32; ++q) {
+                    const int64_t col = j0 + c0 + q;
+                    if (col < a.N) {
+                        const float acc = (nit > 0) ? __uint_as_float(v[q]) : 0.f;
+                        if (a.ksplit == 1) {
+                            float* cp = a.C + row * a.sc_i + col * a.sc_j;
+                            *cp = (a.beta == 0.f) ? a.alpha * acc : a.alpha * acc + a.beta * (*cp);
+                        } else {
+                            a.partial[((size_t) ks * a.Npad + col) * a.Mpad + row] = acc;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (a.cl > 1) cluster_sync_all();                      // no CTA leaves while peers may still write to it or signal it
+    if (warp == 1) tmem_dealloc(tmem_d, TC_BN);
+}
+
+__global__ void __launch_bounds__(256) tc_reduce_kernel(const float* __restrict__ partial, int ksplit, int64_t M, int64_t N, int64_t Mpad, int64_t Npad,
+                                                      float alpha, float beta, float* __restrict__ C, int64_t sc_i, int64_t sc_j) {
+    const int64_t total = M * N;
+    for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t col = e / M, row = e - col * M;
+        float s = 0.f;
+        for (int p = 0; p < ksplit; ++p) s += partial[((size_t) p * Npad + col) * Mpad + row];
+        float* c = C + row * sc_i + col * sc_j;
+        *c = (beta == 0.f) ? alpha * s : alpha * s + beta * (*c);
+    }
+}
+
+int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
+    if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
+    if (g.Sx != nullptr || !g.l_on_cols || (g.w.pc0 & 3) != 0) return RBX_ERR_UNSUPPORTED;
+    if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 64 || g.N < 64 || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
+    if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;
+    if (g.alpha == 0.f) return launch_scale_view<float>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
+
+    CUtensorMap tmap;
+    if (!make_tmap_2d(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, g.X, (uint64_t) g.K, (uint64_t) g.N, (uint64_t) g.sx_j * 4, TC_BK, TC_BN,
+                      CU_TENSOR_MAP_SWIZZLE_128B))
+        return RBX_ERR_UNSUPPORTED;
+
+    TcArgs a;
+    a.w = g.w; a.M = g.M; a.N = g.N; a.K = g.K; a.alpha = g.alpha; a.beta = g.beta; a.C = g.C; a.sc_i = g.sc_i; a.sc_j = g.sc_j;
+    const int tiles_m = (int)((g.M + TC_BM - 1) / TC_BM);
+    a.tiles_n = (int)((g.N + TC_BN - 1) / TC_BN);
+    a.nk = (int)((g.K + TC_BK - 1) / TC_BK);
+    const int tiles = tiles_m * a.tiles_n;
+    int ksplit = (2 * kNumSMs) / tiles;                    // about two waves of CTAs
+    if (ksplit > a.nk / 8) ksplit = a.nk / 8;
+    if (ksplit < 1) ksplit = 1;
+    if (const char* ev = getenv("RBX_TC_KSPLIT")) { const int v = atoi(ev); if (v >= 1 && v <= a.nk) ksplit = v; }
+    a.ksplit = ksplit;
+    a.dbg = getenv("RBX_TC_DBG") ? atoi(getenv("RBX_TC_DBG")) : 0;
+    a.Mpad = (g.M + 31) & ~(int64_t) 31; a.Npad = g.N;
+    a.partial = nullptr;
+    if (ksplit > 1 && cudaMallocAsync(&a.partial, sizeof(float) * (size_t) ksplit * a.Mpad * a.Npad, stream) != cudaSuccess) {
+        cudaGetLastError();
+        return RBX_ERR_ALLOC;
+    }
+    auto kern = g.w.family == 'G' ? sketch_dense_tc_kernel<'G'> : sketch_dense_tc_kernel<'U'>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) TC_SMEM);
+    // Cluster sharing of the generated operator tile works (parity-tested with RBX_TC_CLUSTER=2/4) but measured slower and
+    // erratic on B200 (lock-step coupling of the CTAs + cluster wave quantisation), so it is opt-in for now.
+    a.cl = 1;
+    if (const char* ev = getenv("RBX_TC_CLUSTER")) { const int v = atoi(ev); if ((v == 1 || v == 2 || v == 4) && a.tiles_n % v == 0) a.cl = v; }
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(tiles * ksplit)); cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = TC_SMEM; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned) a.cl; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        if (cudaLaunchKernelEx(&cfg, kern, tmap, a) != cudaSuccess) { cudaGetLastError(); if (a.partial) cudaFreeAsync(a.partial, stream); return RBX_ERR_CUDA; }
+    }
+    count_launch();
+    int rc = check_launch("sketch_dense_tc_kernel");
+    if (rc == RBX_OK && ksplit > 1) {
+        int64_t blocks = (g.M * g.N + 255) / 256;
+        if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+        tc_reduce_kernel<<<(unsigned) blocks, 256, 0, stream>>>(a.partial, ksplit, g.M, g.N, a.Mpad, a.Npad, g.alpha, g.beta, g.C, g.sc_i, g.sc_j);
+        count_launch();
+        rc = check_launch("tc_reduce_kernel");
+    }
+    if (a.partial) cudaFreeAsync(a.partial, stream);
+    return rc;
+}
+
+int launch_sketch_dense_tc_f64(const GemmOperands<double>&, cudaStream_t) { return RBX_ERR_UNSUPPORTED; }
+
+}  // namespace rbx

@@ -122,6 +122,28 @@ def test_sketch_general_dense_medium_ragged(rb, cuda, dt):
         run_dense_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, 1.0, 0.0, off=off, D_extra=(3, 5))
 
 
+def test_sketch_general_dense_tensor_core_path(rb, cuda):
+    """float problems inside the tcgen05 kernel's envelope (rbx_sketch_dense_tc.cu): ragged M / N / K, operator offsets,
+    alpha / beta, both families, and the right-sketch form that maps onto it. The launch count proves the path taken
+    (tensor-core kernel + split-K reduce = 2 launches; the SIMT kernel is 1)."""
+    cases = [("L", "C", "N", "N", 256, 300, 4100, 1.0, 0.0, (0, 0), "G"),
+             ("L", "C", "N", "N", 200, 260, 4096, 1.5, -0.5, (5, 8), "G"),
+             ("L", "C", "N", "N", 128, 512, 2052, 1.0, 0.0, (0, 4), "U"),
+             ("R", "R", "N", "N", 256, 300, 4100, 1.0, 2.0, (0, 0), "G"),
+             ("L", "R", "N", "T", 256, 256, 4096, 1.0, 0.0, (0, 0), "U")]
+    for (side, layout, opS, opA, d, n, m, alpha, beta, off, fam) in cases:
+        l0 = rb.lib.rbx_launch_count()
+        ro, co = off
+        if side == "R":
+            # B (n x d) = A (n x m) * S (m x d): operator offsets are (rows, cols) of the tall S; its parent is S^T
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, m, n, alpha, beta, off=(co, ro), D_extra=(8, 3), fam=fam)
+        else:
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, n, m, alpha, beta, off=(ro, co), D_extra=(3, 8), fam=fam)
+        launches = rb.lib.rbx_launch_count() - l0
+        assert launches == 2, f"expected the tensor-core kernel + reduce, saw {launches} launch(es) for {(side, layout, d, n, m)}"
+        assert ratio < 0.05      # 3xTF32 with FP32 accumulation sits far inside the FP32 GEMM bound
+
+
 def test_nan_in_B_is_overwritten_when_beta_is_zero(rb, cuda):
     """util::safe_scal (util.hh:51-59) / BLAS convention: beta == 0 never reads B"""
     S = rb.DenseSkOp(rb.DenseDist(4, 9), 1)
