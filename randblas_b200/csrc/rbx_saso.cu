@@ -258,7 +258,10 @@ __device__ __forceinline__ uint32_t ld_code(const uint32_t* p, bool in_smem) {
     return v;
 }
 
-constexpr int SASO_NU = 3;          // elements of a slot handled by predicated straight-line code; the rest loop
+#ifndef SASO_NU_VAL
+#define SASO_NU_VAL 3
+#endif
+constexpr int SASO_NU = SASO_NU_VAL;          // elements of a slot handled by predicated straight-line code; the rest loop
 
 // slots [0, NS) of this warp: acc[s] += sum of the gathered (signed) A values of its elements.
 // codes: this lane's first code (step = codes per element); lanebase: shared address of this lane's column in row 0 of

@@ -12,7 +12,7 @@
 //    exact in FP32) and D += hi*hi + lo*hi + hi*lo with FP32 accumulation in TMEM; the dropped lo*lo term is 2^-22
 //    relative, inside the reference's own GEMM tolerance (test/comparison.hh).
 //  * warp roles: warp 0 = TMA producer for X (cp.async.bulk.tensor, 128B swizzle), warp 1 = TMEM allocator + single
-//    MMA-issuing thread, warps 2..9 = generators: bit-exact Philox/Box-Muller (rbx_rng.cuh) -> hi/lo split -> swizzled
+//    MMA-issuing thread, warps 2..17 = generators: bit-exact Philox/Box-Muller (rbx_rng.cuh) -> hi/lo split -> swizzled
 //    K-major operand layout, then the hi/lo split of the X tile in place; they are also the epilogue warps
 //    (tcgen05.ld -> alpha/beta -> global, or split-K partials summed in a fixed order by a second kernel).
 //  * the CTAs of one row block (same operator rows, different columns of X) form a thread-block cluster of up to 4:
@@ -32,7 +32,7 @@ namespace rbx {
 constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32;
 constexpr int TC_XST = 3;           // raw / hi X tiles in flight (hides the TMA latency)
 constexpr int TC_LST = 2;           // operator (hi + lo) tiles and X_lo tiles (produced on chip, one stage ahead is enough)
-constexpr int TC_GEN_WARPS = 8, TC_THREADS = (2 + TC_GEN_WARPS) * 32;
+constexpr int TC_GEN_WARPS = 16, TC_THREADS = (2 + TC_GEN_WARPS) * 32;
 constexpr int TC_S_BYTES = TC_BM * TC_BK * 4;          // 16 KB: one of S_hi / S_lo
 constexpr int TC_X_BYTES = TC_BN * TC_BK * 4;          // 32 KB: one of X_hi / X_lo
 // shared-memory map: [X hi x3][X lo x2][S hi, S lo x2]
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
         }
     } else {
         // ---- generators / converters ----
-        const int gt = tid - 64;                           // 0 .. 255
+        const int gt = tid - 64;                           // 0 .. 32 * TC_GEN_WARPS - 1
         const float scale = (FAMILY == 'U') ? (float) 1.7320508075688772 : 1.0f;
         for (int it = 0; it < nit; ++it) {
             const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
             if (gt == 0) mbar_expect_tx(&ready_s[s], 2 * TC_S_BYTES);      // hi + lo tiles, written by the whole cluster
             const int rows_per = TC_BM / a.cl;                             // operator rows this CTA generates for the cluster
             const uint32_t st_u32 = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES, bar_u32 = smem_u32(&ready_s[s]);
+#pragma unroll 2
             for (int e = gt; e < ((a.dbg & 1) ? 0 : rows_per * (TC_BK / 4)); e += TC_GEN_WARPS * 32) {
                 const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -240,9 +241,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
         mbar_wait(&done, 0);
         tc_fence_after();
         const int lg = warp & 3;                           // TMEM lane quarter this warp may read
-        const int half = (warp - 2) >> 2;                  // which half of the BN columns
+        constexpr int CG = TC_BN / (TC_GEN_WARPS / 4);     // columns per epilogue warp
+        const int cgrp = (warp - 2) >> 2;                  // which group of the BN columns
         const int64_t row = i0 + lg * 32 + lane;
-        for (int c0 = half * (TC_BN / 2); c0 < (half + 1) * (TC_BN / 2); c0 += 32) {
+        for (int c0 = cgrp * CG; c0 < (cgrp + 1) * CG; c0 += 32) {
             uint32_t v[32];
             tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t) c0, v);
             if (row < a.M) {

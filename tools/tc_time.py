@@ -12,7 +12,7 @@ for fam in sys.argv[1:] or ["G", "U"]:
     f = lambda: rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A, m, 0.0, C, d)
     f(); torch.cuda.synchronize()
     ts = []
-    for _ in range(8):
+    for _ in range(int(os.environ.get("REPS","8"))):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); f(); e1.record(); torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
