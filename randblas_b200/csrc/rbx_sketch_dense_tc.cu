@@ -32,6 +32,7 @@ namespace rbx {
 constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32;
 constexpr int TC_XST = 3;           // raw / hi X tiles in flight (hides the TMA latency)
 constexpr int TC_LST = 2;           // operator (hi + lo) tiles and X_lo tiles (produced on chip, one stage ahead is enough)
+constexpr int TC_EPI_WARPS = 16;     // generator warps that also run the epilogue (a multiple of 4)
 constexpr int TC_GEN_WARPS = 16, TC_THREADS = (2 + TC_GEN_WARPS) * 32;
 constexpr int TC_S_BYTES = TC_BM * TC_BK * 4;          // 16 KB: one of S_hi / S_lo
 constexpr int TC_X_BYTES = TC_BN * TC_BK * 4;          // 32 KB: one of X_hi / X_lo
@@ -184,19 +185,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
         // ---- generators / converters ----
         const int gt = tid - 64;                           // 0 .. 32 * TC_GEN_WARPS - 1
         const float scale = (FAMILY == 'U') ? (float) 1.7320508075688772 : 1.0f;
-        for (int it = 0; it < nit; ++it) {
-            const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
-            if (u > 0) mbar_wait(&l_empty[s], (u - 1) & 1);
+        // The operator values of stage it+1 are generated into registers while the tensor core works on stage it (after this
+        // warp has handed stage it over), so the FP64-heavy Box-Muller never waits for a shared-memory slot.
+        constexpr int NCH = (TC_BM * (TC_BK / 4) + TC_GEN_WARPS * 32 - 1) / (TC_GEN_WARPS * 32);
+        const int rows_per = TC_BM / a.cl;                 // operator rows this CTA generates for the cluster
+        const int my_chunks = (a.dbg & 1) ? 0 : rows_per * (TC_BK / 4);
+        float4 vals[NCH];
+        auto generate = [&](int it) {
             const int64_t l0 = (int64_t)(kb + it) * TC_BK;
             const int64_t cbase = (a.w.pc0 + l0) >> 2;     // first counter column of this K block (pc0 % 4 == 0)
-            if (gt == 0) mbar_expect_tx(&ready_s[s], 2 * TC_S_BYTES);      // hi + lo tiles, written by the whole cluster
-            const int rows_per = TC_BM / a.cl;                             // operator rows this CTA generates for the cluster
-            const uint32_t st_u32 = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES, bar_u32 = smem_u32(&ready_s[s]);
-#pragma unroll 2
-            for (int e = gt; e < ((a.dbg & 1) ? 0 : rows_per * (TC_BK / 4)); e += TC_GEN_WARPS * 32) {
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+                const int e = gt + q * TC_GEN_WARPS * 32;
                 const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (i0 + r < a.M && l0 + 4 * c < a.K) {
+                if (e < my_chunks && i0 + r < a.M && l0 + 4 * c < a.K) {
                     const Ctr128 ctr = ctr_add(a.w.ctr, (uint64_t)((a.w.pr0 + i0 + r) * a.w.W + cbase + c));
                     v = generate4<FAMILY>(philox4x32_10(ctr, a.w.key), tab);
                     if (FAMILY == 'U') { v.x = __fmul_rn(v.x, scale); v.y = __fmul_rn(v.y, scale); v.z = __fmul_rn(v.z, scale); v.w = __fmul_rn(v.w, scale); }
@@ -204,16 +207,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                     if (l0 + 4 * c + 2 >= a.K) v.z = 0.f;
                     if (l0 + 4 * c + 3 >= a.K) v.w = 0.f;
                 }
-                float4 hi, lo;
-                hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
-                hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
-                hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
-                hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
-                const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
-                for (int p = 0; p < a.cl; ++p) {
-                    const uint32_t dst = mapa_u32(st_u32 + off, (uint32_t) p), bar = mapa_u32(bar_u32, (uint32_t) p);
-                    st_async_v4(dst, hi, bar);
-                    st_async_v4(dst + TC_S_BYTES, lo, bar);
+                vals[q] = v;
+            }
+        };
+        if (nit > 0) generate(0);
+        for (int it = 0; it < nit; ++it) {
+            const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
+            if (u > 0) mbar_wait(&l_empty[s], (u - 1) & 1);
+            if (gt == 0) mbar_expect_tx(&ready_s[s], 2 * TC_S_BYTES);      // hi + lo tiles, written by the whole cluster
+            const uint32_t st_u32 = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES, bar_u32 = smem_u32(&ready_s[s]);
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+                const int e = gt + q * TC_GEN_WARPS * 32;
+                if (e < my_chunks) {
+                    const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
+                    const float4 v = vals[q];
+                    float4 hi, lo;
+                    hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
+                    hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
+                    hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
+                    hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
+                    const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+                    for (int p = 0; p < a.cl; ++p) {
+                        const uint32_t dst = mapa_u32(st_u32 + off, (uint32_t) p), bar = mapa_u32(bar_u32, (uint32_t) p);
+                        st_async_v4(dst, hi, bar);
+                        st_async_v4(dst + TC_S_BYTES, lo, bar);
+                    }
                 }
             }
             if ((a.dbg & 1) && gt == 0) {                  // debug: nothing generated, complete the bytes by hand
@@ -236,15 +255,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
             fence_proxy_async();                           // generic-proxy writes -> visible to the tensor core (async proxy)
             __syncwarp();
             if (lane == 0) mbar_arrive(&ready_x[s]);
+            if (it + 1 < nit) generate(it + 1);
         }
         // ---- epilogue: TMEM -> registers -> global ----
         mbar_wait(&done, 0);
         tc_fence_after();
         const int lg = warp & 3;                           // TMEM lane quarter this warp may read
-        constexpr int CG = TC_BN / (TC_GEN_WARPS / 4);     // columns per epilogue warp
+        constexpr int CG = TC_BN / (TC_EPI_WARPS / 4);     // columns per epilogue warp
         const int cgrp = (warp - 2) >> 2;                  // which group of the BN columns
         const int64_t row = i0 + lg * 32 + lane;
-        for (int c0 = cgrp * CG; c0 < (cgrp + 1) * CG; c0 += 32) {
+        for (int c0 = cgrp * CG; c0 < (cgrp + 1) * CG && warp - 2 < TC_EPI_WARPS; c0 += 32) {
             uint32_t v[32];
             tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t) c0, v);
             if (row < a.M) {
