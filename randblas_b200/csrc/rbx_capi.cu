@@ -251,6 +251,65 @@ static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_h
     return rc;
 }
 
+// Left sketch of a large host matrix, pipelined: op(A) = A (K x N) is cut into row slabs along the contraction axis; slab
+// i+1 crosses PCIe while slab i is sketched with co_s advanced by the slab start and beta = 1 (the first slab carries the
+// caller's beta). Device memory: two slabs instead of all of A. body(k0, klen, A_slab, lda_slab, beta_eff, B_dev, stream).
+template <typename T, typename F>
+static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, const T* A_host, int64_t lda, T beta,
+                             T* B_host, int64_t ldb, F body) {
+    RBX_NEED_DEVICE();
+    const size_t nB = span_elems(layout, rows_B, N, ldb);
+    int64_t klen = (int64_t)((size_t) 512 << 20) / (N * (int64_t) sizeof(T));
+    klen = (klen / 512) * 512;
+    if (klen < 512) klen = 512;
+    if (klen > K) klen = K;
+    const int64_t nslab = (K + klen - 1) / klen;
+    T* slab[2] = { nullptr, nullptr }; T* B_dev = nullptr;
+    cudaStream_t sc = nullptr, sx = nullptr;
+    cudaEvent_t copied[2] = { nullptr, nullptr }, consumed[2] = { nullptr, nullptr };
+    int rc = RBX_OK;
+    auto ok = [&](cudaError_t e) { if (e != cudaSuccess && rc == RBX_OK) { cudaGetLastError(); rc = RBX_ERR_CUDA; } return e == cudaSuccess; };
+    if (cudaMalloc(&slab[0], (size_t) klen * N * sizeof(T)) != cudaSuccess || cudaMalloc(&slab[1], (size_t) klen * N * sizeof(T)) != cudaSuccess ||
+        cudaMalloc(&B_dev, nB * sizeof(T)) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
+    if (rc == RBX_OK) {
+        ok(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking)); ok(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b) { ok(cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming)); ok(cudaEventCreateWithFlags(&consumed[b], cudaEventDisableTiming)); }
+    }
+    if (rc == RBX_OK && beta != (T) 0) ok(cudaMemcpyAsync(B_dev, B_host, nB * sizeof(T), cudaMemcpyHostToDevice, sx));
+    for (int64_t i = 0; i < nslab && rc == RBX_OK; ++i) {
+        const int b = (int)(i & 1);
+        const int64_t k0 = i * klen, kl = (k0 + klen < K) ? klen : K - k0;
+        if (i >= 2) ok(cudaStreamWaitEvent(sc, consumed[b], 0));
+        int64_t lda_slab;
+        if (layout == 'C') {        // K x N column-major: slab = kl contiguous elements of each of the N columns
+            lda_slab = kl;
+            ok(cudaMemcpy2DAsync(slab[b], (size_t) kl * sizeof(T), A_host + k0, (size_t) lda * sizeof(T), (size_t) kl * sizeof(T), (size_t) N,
+                                 cudaMemcpyHostToDevice, sc));
+        } else {                    // row-major: kl rows of N elements
+            lda_slab = N;
+            ok(cudaMemcpy2DAsync(slab[b], (size_t) N * sizeof(T), A_host + k0 * lda, (size_t) lda * sizeof(T), (size_t) N * sizeof(T), (size_t) kl,
+                                 cudaMemcpyHostToDevice, sc));
+        }
+        ok(cudaEventRecord(copied[b], sc));
+        ok(cudaStreamWaitEvent(sx, copied[b], 0));
+        if (rc == RBX_OK) rc = body(k0, kl, (const T*) slab[b], lda_slab, i == 0 ? beta : (T) 1, B_dev, (void*) sx);
+        ok(cudaEventRecord(consumed[b], sx));
+    }
+    if (rc == RBX_OK) ok(cudaMemcpyAsync(B_host, B_dev, nB * sizeof(T), cudaMemcpyDeviceToHost, sx));
+    if (sx) ok(cudaStreamSynchronize(sx));
+    if (sc) ok(cudaStreamSynchronize(sc));
+    for (int b = 0; b < 2; ++b) { if (copied[b]) cudaEventDestroy(copied[b]); if (consumed[b]) cudaEventDestroy(consumed[b]); }
+    if (sc) cudaStreamDestroy(sc);
+    if (sx) cudaStreamDestroy(sx);
+    cudaFree(slab[0]); cudaFree(slab[1]); cudaFree(B_dev);
+    return rc;
+}
+// the pipelined path applies to plain left sketches of a host matrix of at least 1 GiB
+template <typename T>
+static inline bool use_slabs(char side, char opS, char opA, int64_t N, int64_t K) {
+    return side == 'L' && opS == 'N' && opA == 'N' && (double) N * (double) K * sizeof(T) >= (double)((size_t) 1 << 30) && !getenv("RBX_NO_SLABS");
+}
+
 static inline void host_dims(char side, char opA, int64_t p0, int64_t p1, int64_t p2,
                              int64_t* rows_A, int64_t* cols_A, int64_t* rows_B, int64_t* cols_B) {
     if (side == 'L') { const int64_t d = p0, n = p1, m = p2; *rows_A = (opA == 'N') ? m : n; *cols_A = (opA == 'N') ? n : m; *rows_B = d; *cols_B = n; }
@@ -487,6 +546,14 @@ int rbx_host_sketch_sparseop_##SUF(char side, char layout, char opS, char opA, i
                                    T* B_host, int64_t ldb) {                                                                      \
     int64_t rA, cA, rB, cB;                                                                                                       \
     host_dims(side, opA, p0, p1, p2, &rA, &cA, &rB, &cB);                                                                         \
+    if (use_slabs<T>(side, opS, opA, p1, p2)) {                                                                                   \
+        { DryRun dry; RBX_TRY(sketch_sparseop<T>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, vec_nnz, major_axis,  \
+                                                 ctr, key, ro_s, co_s, (const T*) nullptr, lda, beta, (T*) nullptr, ldb, nullptr)); } \
+        return staged_left_slabs<T>(layout, p0, p1, p2, A_host, lda, beta, B_host, ldb,                                           \
+            [&](int64_t k0, int64_t kl, const T* A_slab, int64_t lda_slab, T beta_eff, T* B_dev, void* st) {                      \
+                return sketch_sparseop<T>(side, layout, opS, opA, p0, p1, kl, alpha, S_rows, S_cols, vec_nnz, major_axis, ctr,    \
+                                          key, ro_s, co_s + k0, A_slab, lda_slab, beta_eff, B_dev, ldb, st); });                   \
+    }                                                                                                                             \
     return with_staged<T>(layout, rA, cA, A_host, lda, rB, cB, B_host, ldb, beta != (T) 0,                                        \
         [&](const T* A_dev, T* B_dev, void* st) {                                                                                 \
             return sketch_sparseop<T>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, vec_nnz, major_axis, ctr, key,   \

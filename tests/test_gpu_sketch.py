@@ -390,3 +390,21 @@ def test_host_pointer_entry_points(rb, cuda):
     rb.fill_dense(rb.DenseDist(16, 300), buf, rb.RNGState(3))
     rc, exp, _ = ol.fill_dense("f32", "R", 16, 300, "G", "L", 16, 300, 0, 0, [0, 0, 0, 0], [3, 0])
     assert np.array_equal(buf.numpy().view(np.uint32), exp.view(np.uint32))
+
+
+@pytest.mark.parametrize("layout", ["C", "R"])
+def test_host_pointer_pipelined_slabs(rb, cuda, layout):
+    """host matrices of >= 1 GiB are sketched slab by slab (copy of slab i+1 overlaps the sketch of slab i, co_s advanced per
+    slab, beta carried by the first slab): same result as the device-resident call up to the summation order"""
+    d, n, m = 256, 1024, (1 << 17) + 1000            # 1 GiB + a ragged last slab
+    A = torch.empty(m * n, dtype=torch.float64, device=cuda)
+    rb.fill_dense(rb.Layout(layout), rb.DenseDist(m, n), m, n, 0, 0, A, rb.RNGState(99))
+    lda, ldb = (m, d) if layout == "C" else (n, n)
+    S = rb.SparseSkOp(rb.SparseDist(d, m + 24, 8), 1997)
+    B0 = torch.ones(d * n, dtype=torch.float64)
+    Bd = B0.to(cuda)
+    rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.5, S, 0, 24, A, lda, -0.5, Bd, ldb)
+    Bh = B0.clone()
+    rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.5, S, 0, 24, A.cpu(), lda, -0.5, Bh, ldb)
+    scale = float(Bd.abs().max())
+    assert float((Bh - Bd.cpu()).abs().max()) <= 1e-12 * scale
