@@ -12,17 +12,19 @@
 //     an XOR-swizzled transposing store for column-contiguous data -- the ring layout is the same for both);
 //   * accumulator registers cannot be indexed dynamically, so the operator is delivered SORTED BY ROW: a prep kernel
 //     regenerates each CK-column chunk of S on the device (bit-exact Fisher-Yates, rbx_fy.cuh), sorts its entries by
-//     (row, column) and emits, per warp, a stream of 32-bit codes (ring byte offset of the A row | sign << 31) plus a
-//     count per accumulator slot. The main loop is a statically unrolled walk over the slots with a dynamic trip count
-//     per slot: one broadcast LDS (code), one 128-byte gather LDS, one FP add. No atomics, no shared-memory
-//     read-modify-write, fixed summation order => run-to-run identical results;
-//   * double precision: the two half-warps work on different rows; the prep kernel pairs their streams and pads the
-//     shorter with a code that points at a zero row of the ring;
+//     (row, column) and emits one 16-byte RECORD per accumulator slot: the first three 32-bit codes of the row (ring
+//     offset of the A row | sign << 31) and the entry count; the rare entries beyond three go to a small tail region.
+//     The main loop is a statically unrolled walk over the slots: one broadcast LDS.128 (record), then per entry one
+//     128-byte gather LDS, one sign flip, one FP add. Nothing in the loop depends on a global load. No atomics, no
+//     shared-memory read-modify-write, fixed summation order => run-to-run identical results;
+//   * double precision: the two half-warps work on different rows, each with its own record; a row with fewer entries
+//     than its partner is padded with a code that points at a zero row of the ring;
 //   * the row blocks (d / 1024) of one column segment are adjacent CTAs and re-read the A chunk through L2, so HBM
 //     sees each byte of A once.
 // Rejected after measurement: TMA boxes for the A chunk (256-byte box rows are TMA row-rate bound, ~28 cycles/row),
 // cluster multicast (73 cycles/row), register tiles selected with brx.idx (~45 issue slots per select), B tile in
 // shared memory with read-modify-write (latency bound at 16 warps/SM, 24 B of shared-memory traffic per update).
+#include <cmath>
 #include <cstdlib>
 #include "rbx_kernels.cuh"
 #include "rbx_fy.cuh"
@@ -35,9 +37,18 @@ constexpr int SASO_WARPS = 16;
 constexpr int SASO_RW = 64;         // rows of B per warp
 constexpr int SASO_R = SASO_WARPS * SASO_RW;   // rows of B per CTA
 constexpr int SASO_THREADS = SASO_WARPS * 32;
-constexpr int SASO_NST = 3;         // ring stages
-constexpr int SASO_PAD = 4;         // zero codes after each row block's stream (read-ahead of the main loop)
+// ring stages: row-contiguous data runs two long chunks (compute per chunk far exceeds the copy latency, and a longer
+// chunk means more entries per accumulator slot); the slower element-wise copy of column-contiguous data wants three
+constexpr int SASO_NST_ROWS = 2, SASO_NST_COLS = 3;
 constexpr uint32_t SASO_SIGN = 0x80000000u;
+#ifndef SASO_NU_VAL
+#define SASO_NU_VAL 3
+#endif
+constexpr int SASO_NU = SASO_NU_VAL;          // codes held by a slot record; the rest of a slot's elements are its tail
+#ifndef SASO_GROUP
+#define SASO_GROUP 4      // slots whose records and gathers are in flight together
+#endif
+static_assert(SASO_NU == 3, "the 16-byte slot record holds three codes and the count");
 
 // exclusive scan of in[0..n) into out[0..n], out[n] = total; all SASO_THREADS threads of the block call it
 __device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* out, int n, uint32_t* wtot) {
@@ -65,16 +76,21 @@ __device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* ou
 }
 
 // ---- prep: one block per chunk of CK columns of S -----------------------------------------------------------
-// Outputs, per chunk:
-//   stream[chunk * stream_stride + ...]  elements of HALVES codes; element e of slot q is at ws-relative position pos(q)+e
-//   cnt[chunk * cnt_stride + q]          elements in slot q (q = bucket * NS + s; rows bucket*64 + h*NS + s, h < HALVES)
-//   ws[chunk * ws_stride + b]            first element of bucket b (b = 0 .. nbuckets), row blocks start 16-byte aligned
-//                                        and are followed by >= SASO_PAD zero elements
+// Slot q = bucket * NS + s owns rows bucket*64 + h*NS + s, h < HALVES (the half-warps of a double-precision warp work on
+// different rows). n(q) = max over h of the row's entry count in this chunk. Outputs, per chunk:
+//   rec[chunk * rec_stride + (q * HALVES + h) * 4 ..]   one 16-byte record per (slot, half): the row's first SASO_NU
+//        codes (zero code where it has fewer) and n(q). The record of a bucket's slot 0 also carries, above bit 12, where
+//        the bucket's tail codes start inside its row block's region, and in bit 31 "not in the region";
+//   stream[chunk * stream_stride + (rb * cap + ...) * HALVES + h]   region of row block rb: the tails (elements SASO_NU ..
+//        n(q)-1, HALVES codes per element, the shorter row padded with the zero code) of its buckets, bucket after bucket,
+//        as long as they fit in cap elements. The main kernel copies the region into the ring stage;
+//   stream[chunk * stream_stride + (nrb * cap + ws[b] + ...) * HALVES + h]   the tails of buckets that did not fit (far
+//        tail of the distribution), read straight from global memory; ws[chunk * ws_stride + b] = their start.
 template <int KMAX, int HALVES>
 __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key64 key, int vec_nnz, int64_t dim_major, int64_t ro, int64_t co,
-                                                               int64_t M, int64_t K, int CK, int nbuckets, int nrb, int cols_contig,
+                                                               int64_t M, int64_t K, int CK, int nbuckets, int nrb, int cols_contig, int cap,
                                                                uint32_t* __restrict__ stream, int stream_stride,
-                                                               uint16_t* __restrict__ cnt, int cnt_stride,
+                                                               uint32_t* __restrict__ rec, int rec_stride,
                                                                uint32_t* __restrict__ ws, int ws_stride) {
     constexpr int NS = SASO_RW / HALVES;
     extern __shared__ uint32_t sh32[];
@@ -87,7 +103,8 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     uint32_t* rowcnt = rowoff + Mp + 1;      // Mp
     uint32_t* slotcnt = rowcnt + Mp;         // nslots
     uint32_t* slotoff = slotcnt + nslots;    // nslots + 1
-    uint16_t* trow = reinterpret_cast<uint16_t*>(slotoff + nslots + 1);   // E
+    uint32_t* tailcnt = slotoff + nslots + 1;   // nslots
+    uint16_t* trow = reinterpret_cast<uint16_t*>(tailcnt + nslots);       // E
     const int64_t chunk = blockIdx.x;
     // a code is the ring offset of A row c in elements: c * (row pitch / sizeof(T)); the pitch is 128 bytes, plus one
     // element when the data is column-contiguous (see saso_tile_kernel). Row CK of the ring is all zeros.
@@ -95,7 +112,6 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     const uint32_t zero_code = (uint32_t) CK * pitch_el;
 
     uint32_t* so = stream + chunk * stream_stride;
-    for (int e = t; e < stream_stride; e += SASO_THREADS) so[e] = zero_code;
     for (int r = t; r < Mp; r += SASO_THREADS) rowcnt[r] = 0;
     for (int e = t; e < E; e += SASO_THREADS) trow[e] = 0xFFFF;
     __syncthreads();
@@ -138,42 +154,60 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
 #pragma unroll
         for (int h = 0; h < HALVES; ++h) { const uint32_t v = rowcnt[b * SASO_RW + h * NS + s]; n = v > n ? v : n; }
         slotcnt[q] = n;
+        tailcnt[q] = n > (uint32_t) SASO_NU ? n - (uint32_t) SASO_NU : 0u;
     }
     __syncthreads();
-    block_excl_scan(slotcnt, slotoff, nslots, wtot);
-    // shift of each row block: aligned start, SASO_PAD zero elements after the previous block
-    uint32_t shift[4] = { 0, 0, 0, 0 };
-    for (int rb = 1; rb < nrb; ++rb) {
-        const uint32_t raw = slotoff[rb * SASO_WARPS * NS];
-        shift[rb] = ((raw + shift[rb - 1] + SASO_PAD + 3u) & ~3u) - raw;
+    block_excl_scan(tailcnt, slotoff, nslots, wtot);
+    // first tail element of each row block, and whether any bucket of the chunk spills out of its region
+    uint32_t rb_base[4];
+    bool any_spill = false;
+    for (int rb = 0; rb < 4; ++rb) {
+        const int q0 = rb * SASO_WARPS * NS, q1 = (rb + 1) * SASO_WARPS * NS;
+        rb_base[rb] = slotoff[q0 < nslots ? q0 : nslots];
+        any_spill = any_spill || (slotoff[q1 < nslots ? q1 : nslots] - rb_base[rb] > (uint32_t) cap);
     }
-    uint16_t* co_ = cnt + chunk * cnt_stride;
-    for (int q = t; q < cnt_stride; q += SASO_THREADS) co_[q] = q < nslots ? (uint16_t) slotcnt[q] : (uint16_t) 0;
+    const uint32_t region_words = (uint32_t)(nrb * cap * HALVES);
+    for (uint32_t e = t; e < region_words; e += SASO_THREADS) so[e] = zero_code;
+    if (any_spill) {
+        const uint32_t used = slotoff[nslots] * HALVES;
+        for (uint32_t e = t; e < used; e += SASO_THREADS) so[region_words + e] = zero_code;
+    }
     uint32_t* wo = ws + chunk * ws_stride;
-    for (int b = t; b <= nbuckets; b += SASO_THREADS) {
-        const int rb = b < nbuckets ? b / SASO_WARPS : nrb - 1;
-        wo[b] = slotoff[b * NS] + shift[rb];
-    }
-    for (int q = t; q < nslots; q += SASO_THREADS) {
-        const int b = q / NS, s = q % NS;
-        const uint32_t n = slotcnt[q], p = slotoff[q] + shift[b / SASO_WARPS];
+    for (int b = t; b <= nbuckets; b += SASO_THREADS) wo[b] = slotoff[b * NS];
+    __syncthreads();
+    uint32_t* ro_ = rec + chunk * rec_stride;
+    for (int q = t; q < rec_stride / (4 * HALVES); q += SASO_THREADS) {
+        const bool live = q < nslots;
+        const int b = q / NS, s = q % NS, rb = b / SASO_WARPS;
+        uint32_t n = 0, w = 0;
+        uint32_t* tails = so;
+        if (live) {
+            n = slotcnt[q];
+            const uint32_t b_start = slotoff[b * NS] - rb_base[rb], b_end = slotoff[(b + 1) * NS] - rb_base[rb];
+            const bool fits = b_end <= (uint32_t) cap;
+            tails = fits ? so + ((size_t) rb * cap + (slotoff[q] - rb_base[rb])) * HALVES : so + region_words + (size_t) slotoff[q] * HALVES;
+            w = n | (s == 0 ? ((fits ? b_start << 12 : SASO_SIGN)) : 0u);
+        }
 #pragma unroll
         for (int h = 0; h < HALVES; ++h) {
             const int row = b * SASO_RW + h * NS + s;
-            const uint32_t nr = rowcnt[row];
-            const uint32_t* src = sorted + rowoff[row];
-            for (uint32_t i = 0; i < nr; ++i) so[(p + i) * HALVES + h] = src[i];
+            const uint32_t nr = live ? rowcnt[row] : 0u;
+            const uint32_t* src = sorted + (live ? rowoff[row] : 0u);
+            uint32_t r4[3];
+#pragma unroll
+            for (int i = 0; i < SASO_NU; ++i) r4[i] = (uint32_t) i < nr ? src[i] : zero_code;
+            *reinterpret_cast<uint4*>(ro_ + ((size_t) q * HALVES + h) * 4) = make_uint4(r4[0], r4[1], r4[2], w);
+            for (uint32_t i = SASO_NU; i < nr; ++i) tails[(i - SASO_NU) * HALVES + h] = src[i];
         }
-        (void) n;
     }
 }
 
 template <typename T>
 struct SasoArgs {
     const T* X; int64_t sx_l, sx_j; int64_t K, N;      // data view: X[l * sx_l + j * sx_j], one of the strides is 1
-    const uint32_t* stream; const uint16_t* cnt; const uint32_t* ws;
-    int stream_stride, cnt_stride, ws_stride;
-    int CK, cap;                                       // rows per chunk; stream elements a ring stage can hold
+    const uint32_t* stream; const uint32_t* rec; const uint32_t* ws;
+    int stream_stride, rec_stride, ws_stride;
+    int CK, cap;                                       // rows per chunk; tail elements a row block's region holds
     int nbuckets, njb, nrb, msplit, nchunks, dbg_skip;
     int64_t M;
     T alpha, beta;
@@ -191,21 +225,7 @@ template <int BYTES> __device__ __forceinline__ void cp_async_small(uint32_t dst
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-// acc += (i < n) ? (+/-) *(T*)addr : 0, sign taken from bit 31 of code; a predicated load, no branch
-template <typename T> __device__ __forceinline__ void gather_add_if(T& acc, uint32_t addr, uint32_t code, int n, int i);
-template <> __device__ __forceinline__ void gather_add_if<double>(double& acc, uint32_t addr, uint32_t code, int n, int i) {
-    unsigned long long bits;
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.gt.s32 p, %2, %3;\n\tmov.b64 %0, 0;\n\t@p ld.shared.b64 %0, [%1];\n\t}"
-                 : "=l"(bits) : "r"(addr), "r"(n), "r"(i));
-    const double v = __longlong_as_double((long long) bits);
-    acc += __hiloint2double(__double2hiint(v) ^ (int)(code & SASO_SIGN), __double2loint(v));
-}
-template <> __device__ __forceinline__ void gather_add_if<float>(float& acc, uint32_t addr, uint32_t code, int n, int i) {
-    uint32_t bits;
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.gt.s32 p, %2, %3;\n\tmov.b32 %0, 0;\n\t@p ld.shared.b32 %0, [%1];\n\t}"
-                 : "=r"(bits) : "r"(addr), "r"(n), "r"(i));
-    acc += __uint_as_float(bits ^ (code & SASO_SIGN));
-}
+// (+/-) *(T*)addr from shared memory, the sign taken from bit 31 of code
 template <typename T> __device__ __forceinline__ T lds_signed(uint32_t addr, uint32_t code);
 template <> __device__ __forceinline__ double lds_signed<double>(uint32_t addr, uint32_t code) {
     double v;
@@ -219,82 +239,73 @@ template <> __device__ __forceinline__ float lds_signed<float>(uint32_t addr, ui
                  : "=f"(v) : "r"(addr), "r"(code));
     return v;
 }
-// elements first .. n-1 of a slot whose codes sit in shared memory at code_addr, code_addr + step_bytes, ...:
-// acc += (+/-) A value. A warp-uniform loop (bra.uni: no reconvergence bookkeeping).
-template <typename T> __device__ __forceinline__ void slot_tail(T& acc, uint32_t code_addr, int first, int n, uint32_t lanebase, int step_bytes);
-template <> __device__ __forceinline__ void slot_tail<double>(double& acc, uint32_t code_addr, int first, int n, uint32_t lanebase, int step_bytes) {
-    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 i, ca, code, a, lo, hi;\n\t.reg .f64 v;\n\t"
-                 "setp.le.s32 p, %3, %2;\n\t@p bra.uni TAIL_DONE;\n\t"
-                 "mov.b32 i, %2;\n\tmov.b32 ca, %1;\n"
-                 "TAIL_LOOP:\n\t"
-                 "ld.shared.b32 code, [ca];\n\t"
-                 "shl.b32 a, code, 3;\n\tadd.u32 a, a, %4;\n\t"
-                 "ld.shared.v2.b32 {lo, hi}, [a];\n\t"
-                 "lop3.b32 hi, hi, code, 0x80000000, 0x78;\n\t"
-                 "mov.b64 v, {lo, hi};\n\tadd.f64 %0, %0, v;\n\t"
-                 "add.u32 ca, ca, %5;\n\tadd.s32 i, i, 1;\n\tsetp.lt.s32 p, i, %3;\n\t@p bra.uni TAIL_LOOP;\n"
-                 "TAIL_DONE:\n\t}"
-                 : "+d"(acc) : "r"(code_addr), "r"(first), "r"(n), "r"(lanebase), "r"(step_bytes));
-}
-template <> __device__ __forceinline__ void slot_tail<float>(float& acc, uint32_t code_addr, int first, int n, uint32_t lanebase, int step_bytes) {
-    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 i, ca, code, a, x;\n\t.reg .f32 v;\n\t"
-                 "setp.le.s32 p, %3, %2;\n\t@p bra.uni TAIL_DONE;\n\t"
-                 "mov.b32 i, %2;\n\tmov.b32 ca, %1;\n"
-                 "TAIL_LOOP:\n\t"
-                 "ld.shared.b32 code, [ca];\n\t"
-                 "shl.b32 a, code, 2;\n\tadd.u32 a, a, %4;\n\t"
-                 "ld.shared.b32 x, [a];\n\t"
-                 "lop3.b32 x, x, code, 0x80000000, 0x78;\n\t"
-                 "mov.b32 v, x;\n\tadd.f32 %0, %0, v;\n\t"
-                 "add.u32 ca, ca, %5;\n\tadd.s32 i, i, 1;\n\tsetp.lt.s32 p, i, %3;\n\t@p bra.uni TAIL_LOOP;\n"
-                 "TAIL_DONE:\n\t}"
-                 : "+f"(acc) : "r"(code_addr), "r"(first), "r"(n), "r"(lanebase), "r"(step_bytes));
-}
-// volatile: keeps the code loads where they are written (one slot ahead of their use) instead of all up front
-__device__ __forceinline__ uint32_t ld_code(const uint32_t* p, bool in_smem) {
-    uint32_t v;
-    if (in_smem) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
-    else asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v) : "l"(p));
+// raw bits of *(T*)addr from shared memory, or zero (and no shared-memory access by this lane) when code is the zero code
+template <typename T> struct RawBits;
+template <> struct RawBits<double> { typedef unsigned long long type; };
+template <> struct RawBits<float> { typedef uint32_t type; };
+template <typename T> __device__ __forceinline__ typename RawBits<T>::type lds_raw_nz(uint32_t addr, uint32_t code, uint32_t zero_code);
+template <> __device__ __forceinline__ unsigned long long lds_raw_nz<double>(uint32_t addr, uint32_t code, uint32_t zero_code) {
+    unsigned long long v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, %3;\n\tmov.b64 %0, 0;\n\t@p ld.shared.b64 %0, [%1];\n\t}" : "=l"(v) : "r"(addr), "r"(code), "r"(zero_code));
     return v;
 }
-
-#ifndef SASO_NU_VAL
-#define SASO_NU_VAL 3
-#endif
-constexpr int SASO_NU = SASO_NU_VAL;          // elements of a slot handled by predicated straight-line code; the rest loop
+template <> __device__ __forceinline__ uint32_t lds_raw_nz<float>(uint32_t addr, uint32_t code, uint32_t zero_code) {
+    uint32_t v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, %3;\n\tmov.b32 %0, 0;\n\t@p ld.shared.b32 %0, [%1];\n\t}" : "=r"(v) : "r"(addr), "r"(code), "r"(zero_code));
+    return v;
+}
+__device__ __forceinline__ double apply_sign(unsigned long long bits, uint32_t code) {
+    return __hiloint2double((int)((uint32_t)(bits >> 32) ^ (code & SASO_SIGN)), (int)(uint32_t) bits);
+}
+__device__ __forceinline__ float apply_sign(uint32_t bits, uint32_t code) { return __uint_as_float(bits ^ (code & SASO_SIGN)); }
 
 // slots [0, NS) of this warp: acc[s] += sum of the gathered (signed) A values of its elements.
-// codes: this lane's first code (step = codes per element); lanebase: shared address of this lane's column in row 0 of
-// the stage's A chunk. Address of an element = lanebase + (code << log2(sizeof(T))); the shift drops the sign bit.
-template <typename T, int NS, bool IN_SMEM>
-__device__ __forceinline__ void saso_consume(T (&acc)[NS], const uint32_t* codes, int step, uint32_t lanebase, const uint16_t* cnts) {
+// recs: shared address of this lane's first 16-byte slot record; region: this lane's first code of the row block's tail
+// region in the stage; spill / wsp: where the tails are in global memory when the bucket's did not fit in the region;
+// lanebase: shared address of this lane's column in row 0 of the stage's A chunk. Address of an element =
+// lanebase + (code << log2(sizeof(T))); the shift drops the sign bit.
+// The walk goes G slots at a time: their records, then all of their gathers, are in flight together (4 warps per
+// scheduler cannot hide a record -> gather -> add chain per slot); the tails follow, one (rare) loop per slot.
+template <typename T, int NS, int HALVES>
+__device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, const uint32_t* region, const uint32_t* spill, const uint32_t* wsp,
+                                             uint32_t lanebase, uint32_t zero_code) {
     constexpr int SH = sizeof(T) == 8 ? 3 : 2;
-    uint32_t c[SASO_NU];
+    constexpr int G = SASO_GROUP;
+    typedef typename RawBits<T>::type raw_t;
+    const uint32_t* tp = region;
 #pragma unroll
-    for (int i = 0; i < SASO_NU; ++i) c[i] = ld_code(codes + i * step, IN_SMEM);
+    for (int g = 0; g < NS; g += G) {
+        uint32_t c[G][4];
 #pragma unroll
-    for (int g = 0; g < NS; g += 8) {
-        const uint4 cq = *reinterpret_cast<const uint4*>(cnts + g);
-        const uint32_t cw[4] = { cq.x, cq.y, cq.z, cq.w };
+        for (int j = 0; j < G; ++j)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(c[j][0]), "=r"(c[j][1]), "=r"(c[j][2]), "=r"(c[j][3])
+                         : "r"(recs + (uint32_t)((g + j) * HALVES * 16)));
+        if (g == 0) {
+            const uint32_t w = c[0][3];
+            c[0][3] = w & 0xfffu;
+            tp = (w & SASO_SIGN) ? spill + (size_t) __ldg(wsp) * HALVES : region + ((w >> 12) & 0x7ffffu) * HALVES;
+        }
+        raw_t v[G][SASO_NU];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const int n = (int)((cw[e >> 1] >> (16 * (e & 1))) & 0xffffu);
-            uint32_t addr[SASO_NU], cc[SASO_NU];
+        for (int k = 0; k < SASO_NU; ++k)
 #pragma unroll
-            for (int i = 0; i < SASO_NU; ++i) { cc[i] = c[i]; addr[i] = lanebase + (c[i] << SH); }
-            const uint32_t* cur = codes;
-            codes += n * step;
+            for (int j = 0; j < G; ++j) v[j][k] = lds_raw_nz<T>(lanebase + (c[j][k] << SH), c[j][k], zero_code);
 #pragma unroll
-            for (int i = 0; i < SASO_NU; ++i) c[i] = ld_code(codes + i * step, IN_SMEM);       // next slot's codes
+        for (int k = 0; k < SASO_NU; ++k)
 #pragma unroll
-            for (int i = 0; i < SASO_NU; ++i) gather_add_if<T>(acc[g + e], addr[i], cc[i], n, i);
-            if (IN_SMEM) {
-                slot_tail<T>(acc[g + e], smem_u32(cur + SASO_NU * step), SASO_NU, n, lanebase, step * 4);
-            } else if (n > SASO_NU) {
+            for (int j = 0; j < G; ++j) acc[g + j] += apply_sign(v[j][k], c[j][k]);
+        uint32_t any = 0;
+#pragma unroll
+        for (int j = 0; j < G; ++j) any |= c[j][3];
+        if (any > (uint32_t) SASO_NU) {             // some slot of the group has more than SASO_NU elements
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
 #pragma unroll 1
-                for (int i = SASO_NU; i < n; ++i) {
-                    const uint32_t code = ld_code(cur + i * step, false);
-                    acc[g + e] += lds_signed<T>(lanebase + (code << SH), code);
+                for (uint32_t i = SASO_NU; i < c[j][3]; ++i) {
+                    uint32_t code;
+                    asm volatile("ld.b32 %0, [%1];" : "=r"(code) : "l"(tp));     // generic: the stage's region or global memory
+                    tp += HALVES;
+                    acc[g + j] += lds_signed<T>(lanebase + (code << SH), code);
                 }
             }
         }
@@ -312,14 +323,15 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     constexpr int HALVES = 32 / W;                     // entries per warp instruction: 2 / 1
     constexpr int NS = SASO_RW / HALVES;               // accumulators per lane: 32 doubles / 64 floats
     constexpr int EP = 16 / (int) sizeof(T);           // elements per 16-byte piece
-    constexpr int CNT_BYTES = SASO_WARPS * NS * 2;
+    constexpr int REC_BYTES = SASO_WARPS * NS * HALVES * 16;   // slot records of this CTA's 1024 rows, per chunk
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t smem0 = smem_u32(smem);
     const int CK = a.CK;
     constexpr int PITCH = SASO_ROWB + (COLS_CONTIG ? (int) sizeof(T) : 0);
     const int a_bytes = CK * PITCH;
     const int az_bytes = (a_bytes + PITCH + 15) & ~15;                               // A chunk + its zero row
-    const int stage_bytes = az_bytes + CNT_BYTES + a.cap * HALVES * 4;               // A | zero row | counts | codes
+    const int tail_bytes = a.cap * HALVES * 4;
+    const int stage_bytes = az_bytes + REC_BYTES + tail_bytes;                       // A | zero row | slot records | tail region
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int sub = lane / W, jl = lane % W;
@@ -336,18 +348,18 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     const int cb = COLS_CONTIG ? ms : ms * per;
     const int ce = COLS_CONTIG ? a.nchunks : ((cb + per < a.nchunks) ? cb + per : a.nchunks);
     const int64_t j0 = (int64_t) jb * W;
-    const int b_first = rb * SASO_WARPS;
-    const int b_last = (b_first + SASO_WARPS < a.nbuckets) ? b_first + SASO_WARPS : a.nbuckets;
-    const int bucket = b_first + warp;                 // warp owns rows [bucket*64, bucket*64+64) of the window
+    const int bucket = rb * SASO_WARPS + warp;         // warp owns rows [bucket*64, bucket*64+64) of the window
     const bool active = bucket < a.nbuckets;
 
-    if (tid < SASO_NST * (SASO_ROWB / 8))              // the zero rows of the stages
+    constexpr int NST = COLS_CONTIG ? SASO_NST_COLS : SASO_NST_ROWS;
+    if (tid < NST * (SASO_ROWB / 8))                   // the zero rows of the stages
         *reinterpret_cast<uint2*>(smem + (size_t)(tid / (SASO_ROWB / 8)) * stage_bytes + a_bytes + (tid % (SASO_ROWB / 8)) * 8) = make_uint2(0, 0);
 
-    // A chunk, slot counts and codes of chunk ch -> stage s; [lo, hi) = the row block's range of the code stream
-    // tiles that touch neither edge of A take the copy loops without per-piece bounds arithmetic
+    // A chunk, slot records and tail region of chunk ch -> stage s. Nothing here depends on data read from global
+    // memory: the copies of the next chunk are issued without waiting for anything.
+    // Tiles that touch neither edge of A take the copy loops without per-piece bounds arithmetic.
     const bool cols_inside = j0 + W <= a.N;
-    auto load_async = [&](int ch, int s, uint32_t lo, uint32_t hi) {
+    auto load_async = [&](int ch, int s) {
         const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
         const bool inside = cols_inside && (int64_t)(ch + 1) * CK <= a.K;
         if (!COLS_CONTIG) {
@@ -382,54 +394,39 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
                 }
             }
         }
-        const uint8_t* csrc = reinterpret_cast<const uint8_t*>(a.cnt + (size_t) ch * a.cnt_stride + (size_t) rb * SASO_WARPS * NS);
-        if (tid < CNT_BYTES / 16) cp_async16(st + az_bytes + tid * 16, csrc + tid * 16, 16);
-        uint32_t nel = hi + SASO_PAD - lo;
-        nel = nel > (uint32_t) a.cap ? (uint32_t) a.cap : nel;
-        const int npiece = (int)((nel * HALVES * 4 + 15) / 16);
-        const uint8_t* ssrc = reinterpret_cast<const uint8_t*>(a.stream + (size_t) ch * a.stream_stride + (size_t) lo * HALVES);
-        const uint32_t sdst = st + az_bytes + CNT_BYTES;
-        for (int p = tid; p < npiece; p += SASO_THREADS) cp_async16(sdst + p * 16, ssrc + p * 16, 16);
+        const uint8_t* rsrc = reinterpret_cast<const uint8_t*>(a.rec + (size_t) ch * a.rec_stride) + (size_t) rb * REC_BYTES;
+        for (int p = tid; p < REC_BYTES / 16; p += SASO_THREADS) cp_async16(st + az_bytes + p * 16, rsrc + p * 16, 16);
+        const uint8_t* tsrc = reinterpret_cast<const uint8_t*>(a.stream + (size_t) ch * a.stream_stride) + (size_t) rb * tail_bytes;
+        // the threads that were idle (column-contiguous) or last (row-contiguous) in the A copy take the tail region
+        for (int p = SASO_THREADS - 1 - tid; p < tail_bytes / 16; p += SASO_THREADS) cp_async16(st + az_bytes + REC_BYTES + p * 16, tsrc + p * 16, 16);
     };
-    auto ws_at = [&](int ch, int b) -> uint32_t { return ch < ce ? __ldg(a.ws + (size_t) ch * a.ws_stride + b) : 0u; };
 
-    constexpr int DIST = SASO_NST - 1;                 // prefetch distance in chunks
+    constexpr int DIST = NST - 1;                      // prefetch distance in chunks
     for (int s = 0; s < DIST; ++s) {
-        if (cb + s * cstep < ce) load_async(cb + s * cstep, s, ws_at(cb + s * cstep, b_first), ws_at(cb + s * cstep, b_last));
+        if (cb + s * cstep < ce) load_async(cb + s * cstep, s);
         cp_async_commit();
     }
-    // stream positions, fetched one iteration ahead of their use
-    uint32_t pf_lo = ws_at(cb + DIST * cstep, b_first), pf_hi = ws_at(cb + DIST * cstep, b_last);            // for the next prefetch
-    uint32_t my_lo = ws_at(cb, b_first), my_first = 0, my_end = 0;                             // for the chunk being consumed
-    if (active) { my_first = ws_at(cb, bucket); my_end = ws_at(cb, bucket + 1); }
 
     T acc[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s) acc[s] = (T) 0;
     const uint32_t lx = (uint32_t) jl * (uint32_t) sizeof(T);
+    const uint32_t zero_code = (uint32_t) CK * (uint32_t)(PITCH / (int) sizeof(T));
+    const uint32_t* spill = a.stream + (size_t) a.nrb * a.cap * HALVES + sub;
 
     for (int ch = cb, it = 0; ch < ce; ch += cstep, ++it) {
         cp_async_wait<DIST - 1>();
         __syncthreads();                                // chunk `it` has landed; everyone is done with chunk it-1
         const int nxt = ch + DIST * cstep;
-        if (nxt < ce) load_async(nxt, (it + DIST) % SASO_NST, pf_lo, pf_hi);
+        if (nxt < ce) load_async(nxt, (it + DIST) % NST);
         cp_async_commit();
-        pf_lo = ws_at(nxt + cstep, b_first); pf_hi = ws_at(nxt + cstep, b_last);
-        const uint32_t lo = my_lo, first = my_first, end = my_end;
-        my_lo = ws_at(ch + cstep, b_first);
-        if (active) { my_first = ws_at(ch + cstep, bucket); my_end = ws_at(ch + cstep, bucket + 1); }
         if (active && a.dbg_skip != 1) {
-            const uint32_t st = smem0 + (uint32_t)(it % SASO_NST) * stage_bytes;
-            const uint8_t* st8 = smem + (size_t)(it % SASO_NST) * stage_bytes;
-            const uint16_t* cnts = reinterpret_cast<const uint16_t*>(st8 + az_bytes) + warp * NS;
-            if (end + SASO_PAD - lo <= (uint32_t) a.cap) {
-                const uint32_t* codes = reinterpret_cast<const uint32_t*>(st8 + az_bytes + CNT_BYTES) + (size_t)(first - lo) * HALVES + sub;
-                saso_consume<T, NS, true>(acc, codes, HALVES, st + lx, cnts);
-            } else {
-                // the stage could not hold this warp's codes (far tail of the distribution): read them from global memory
-                const uint32_t* codes = a.stream + (size_t) ch * a.stream_stride + (size_t) first * HALVES + sub;
-                saso_consume<T, NS, false>(acc, codes, HALVES, st + lx, cnts);
-            }
+            const uint32_t st = smem0 + (uint32_t)(it % NST) * stage_bytes;
+            const uint8_t* st8 = smem + (size_t)(it % NST) * stage_bytes;
+            const uint32_t recs = st + az_bytes + (uint32_t)((warp * NS * HALVES + sub) * 16);
+            const uint32_t* region = reinterpret_cast<const uint32_t*>(st8 + az_bytes + REC_BYTES) + sub;
+            saso_consume<T, NS, HALVES>(acc, recs, region, spill + (size_t) ch * a.stream_stride, a.ws + (size_t) ch * a.ws_stride + bucket,
+                                        st + lx, zero_code);
         }
     }
     cp_async_wait<0>();
@@ -463,6 +460,17 @@ __global__ void __launch_bounds__(256) saso_reduce_kernel(const T* __restrict__ 
     }
 }
 
+// Expected number of tail elements (beyond the SASO_NU a record holds) of one slot whose `halves` rows each get a
+// Poisson(lambda) number of entries per chunk: sum over k >= SASO_NU of P(max > k).
+static double saso_mean_tail(double lambda, int halves) {
+    double pmf = exp(-lambda), cdf = pmf, mean = 0.0;
+    for (int k = 1; k < 200; ++k) {
+        if (k > SASO_NU) { double all = 1.0; for (int h = 0; h < halves; ++h) all *= cdf; mean += 1.0 - all; }   // cdf = F(k-1)
+        pmf *= lambda / k; cdf += pmf;
+    }
+    return mean;
+}
+
 template <typename T>
 int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_t S_cols, int64_t vec_nnz, int64_t ro, int64_t co,
                      int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
@@ -484,20 +492,24 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     const int nbuckets = (int)((M + SASO_RW - 1) / SASO_RW);
     const int nrb = (nbuckets + SASO_WARPS - 1) / SASO_WARPS;           // row blocks of 1024 rows
     const int njb = (int)((N + W - 1) / W);
-    // rows of A per chunk: as many as three ring stages (A chunk + the codes that go with it) fit in shared memory
+    // rows of A per chunk: as many as the ring stages (A chunk + the records and tails that go with it) fit in shared memory
     int CK = 0, cap = 0;
+    const size_t nst = cols_contig ? SASO_NST_COLS : SASO_NST_ROWS;
     size_t stage = 0;
-    for (int ck = 512; ck >= 64; ck -= 64) {
-        const double ent_rb = (double) ck * (double) vec_nnz * (double)(M < SASO_R ? M : SASO_R) / (double) S_rows;
-        const int c = (((int)(HALVES == 2 ? ent_rb : 1.25 * ent_rb) + 64) + 31) & ~31;
+    for (int ck = 512; ck >= 64; ck -= (cols_contig ? 16 : 64)) {
+        // tail elements of one row block per chunk: mean + 8 sigma (Poisson tails; sigma^2 < 2 * mean); a bucket that
+        // does not fit reads its tails from global memory
+        const double lambda = (double) ck * (double) vec_nnz / (double) S_rows;
+        const double mean_rb = saso_mean_tail(lambda, HALVES) * SASO_WARPS * NS;
+        const int c = ((int)(mean_rb + 8.0 * sqrt(2.0 * mean_rb + 1.0)) + 32 + 31) & ~31;
         const size_t pitch = SASO_ROWB + (cols_contig ? sizeof(T) : 0);
-        const size_t sb = (((size_t) ck * pitch + pitch + 15) & ~(size_t) 15) + SASO_WARPS * NS * 2 + (size_t) c * HALVES * 4;
-        if (SASO_NST * sb <= SMEM_MAX && (int64_t) ck <= ((K + 63) & ~(int64_t) 63)) { CK = ck; cap = c; stage = sb; break; }
+        const size_t sb = (((size_t) ck * pitch + pitch + 15) & ~(size_t) 15) + (size_t) SASO_WARPS * NS * HALVES * 16 + (size_t) c * HALVES * 4;
+        if (nst * sb <= SMEM_MAX && (int64_t) ck <= ((K + 63) & ~(int64_t) 63)) { CK = ck; cap = c; stage = sb; break; }
     }
-    if (CK == 0) return RBX_ERR_UNSUPPORTED;
+    if (CK == 0 || cap >= (1 << 19)) return RBX_ERR_UNSUPPORTED;
     const int nchunks = (int)((K + CK - 1) / CK);
     const int E = CK * (int) vec_nnz, Mp = nbuckets * SASO_RW, nslots = nbuckets * NS;
-    const size_t prep_smem = (size_t) E * 10 + (size_t)(2 * Mp + 2 * nslots + 2) * 4 + 16;
+    const size_t prep_smem = (size_t) E * 10 + (size_t)(2 * Mp + 3 * nslots + 2) * 4 + 16;
     if (prep_smem > SMEM_MAX) return RBX_ERR_UNSUPPORTED;
     // split the contraction axis so that the grid is several waves of CTAs (one CTA per SM)
     int msplit = (6 * kNumSMs + njb * nrb - 1) / (njb * nrb);
@@ -505,19 +517,19 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     if (msplit < 1) msplit = 1;
     if (const char* ev = getenv("RBX_SASO_MSPLIT")) { const int v = atoi(ev); if (v >= 1 && v <= nchunks) msplit = v; }
 
-    const int stream_stride = ((E + nrb * 8 + SASO_PAD) * HALVES + 3) & ~3;      // codes per chunk
-    const int cnt_stride = nrb * SASO_WARPS * NS;
+    const int stream_stride = ((nrb * cap + E) * HALVES + 3) & ~3;               // tail codes per chunk: regions, then spill
+    const int rec_stride = nrb * SASO_WARPS * NS * HALVES * 4;                  // record words per chunk
     const int ws_stride = (nbuckets + 1 + 3) & ~3;
-    uint32_t* codes = nullptr; uint16_t* cnt = nullptr; uint32_t* ws = nullptr; T* partial = nullptr;
+    uint32_t* codes = nullptr; uint32_t* rec = nullptr; uint32_t* ws = nullptr; T* partial = nullptr;
     const size_t Np = (size_t) njb * W;
     const size_t part_bytes = msplit > 1 ? (size_t) msplit * M * Np * sizeof(T) : 0;
     if (cudaMallocAsync(&codes, (size_t) nchunks * stream_stride * 4, stream) != cudaSuccess ||
-        cudaMallocAsync(&cnt, (size_t) nchunks * cnt_stride * 2, stream) != cudaSuccess ||
+        cudaMallocAsync(&rec, (size_t) nchunks * rec_stride * 4, stream) != cudaSuccess ||
         cudaMallocAsync(&ws, (size_t) nchunks * ws_stride * 4, stream) != cudaSuccess ||
         (part_bytes && cudaMallocAsync(&partial, part_bytes, stream) != cudaSuccess)) {
         cudaGetLastError();
         if (codes) cudaFreeAsync(codes, stream);
-        if (cnt) cudaFreeAsync(cnt, stream);
+        if (rec) cudaFreeAsync(rec, stream);
         if (ws) cudaFreeAsync(ws, stream);
         return RBX_ERR_ALLOC;
     }
@@ -525,29 +537,25 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     {
         auto kern = vec_nnz <= 8 ? saso_prep_kernel<8, HALVES> : saso_prep_kernel<32, HALVES>;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) prep_smem);
-        kern<<<nchunks, SASO_THREADS, prep_smem, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, CK, nbuckets, nrb, cols_contig ? 1 : 0,
-                                                           codes, stream_stride, cnt, cnt_stride, ws, ws_stride);
+        kern<<<nchunks, SASO_THREADS, prep_smem, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, CK, nbuckets, nrb, cols_contig ? 1 : 0, cap,
+                                                           codes, stream_stride, rec, rec_stride, ws, ws_stride);
         count_launch();
         rc = check_launch("saso_prep_kernel");
     }
     if (rc == RBX_OK) {
         SasoArgs<T> a;
         a.X = X; a.sx_l = sx_l; a.sx_j = sx_j; a.K = K; a.N = N;
-        a.stream = codes; a.cnt = cnt; a.ws = ws;
-        a.stream_stride = stream_stride; a.cnt_stride = cnt_stride; a.ws_stride = ws_stride;
+        a.stream = codes; a.rec = rec; a.ws = ws;
+        a.stream_stride = stream_stride; a.rec_stride = rec_stride; a.ws_stride = ws_stride;
         a.CK = CK; a.cap = cap;
         a.nbuckets = nbuckets; a.njb = njb; a.nrb = nrb; a.msplit = msplit; a.nchunks = nchunks;
         a.dbg_skip = getenv("RBX_SASO_SKIP") ? atoi(getenv("RBX_SASO_SKIP")) : 0;
         a.M = M; a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial;
         const unsigned grid = (unsigned)(njb * msplit * nrb);
-        const size_t smem = SASO_NST * stage;
-        if (cols_contig) {
-            cudaFuncSetAttribute(saso_tile_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-            saso_tile_kernel<T, true><<<grid, SASO_THREADS, smem, stream>>>(a);
-        } else {
-            cudaFuncSetAttribute(saso_tile_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-            saso_tile_kernel<T, false><<<grid, SASO_THREADS, smem, stream>>>(a);
-        }
+        const size_t smem = nst * stage;
+        auto tile = cols_contig ? saso_tile_kernel<T, true> : saso_tile_kernel<T, false>;
+        cudaFuncSetAttribute(tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        tile<<<grid, SASO_THREADS, smem, stream>>>(a);
         count_launch();
         rc = check_launch("saso_tile_kernel");
         if (rc == RBX_OK && msplit > 1) {
@@ -558,7 +566,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
             rc = check_launch("saso_reduce_kernel");
         }
     }
-    cudaFreeAsync(codes, stream); cudaFreeAsync(cnt, stream); cudaFreeAsync(ws, stream);
+    cudaFreeAsync(codes, stream); cudaFreeAsync(rec, stream); cudaFreeAsync(ws, stream);
     if (partial) cudaFreeAsync(partial, stream);
     return rc;
 }
