@@ -501,7 +501,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         // does not fit reads its tails from global memory
         const double lambda = (double) ck * (double) vec_nnz / (double) S_rows;
         const double mean_rb = saso_mean_tail(lambda, HALVES) * SASO_WARPS * NS;
-        const int c = ((int)(mean_rb + 8.0 * sqrt(2.0 * mean_rb + 1.0)) + 32 + 31) & ~31;
+        int c = ((int)(mean_rb + 8.0 * sqrt(2.0 * mean_rb + 1.0)) + 32 + 31) & ~31;
+        if (const char* ev = getenv("RBX_SASO_CAP")) { const int v = atoi(ev); if (v >= 0) c = (v + 31) & ~31; }    // tests: force the spill path
         const size_t pitch = SASO_ROWB + (cols_contig ? sizeof(T) : 0);
         const size_t sb = (((size_t) ck * pitch + pitch + 15) & ~(size_t) 15) + (size_t) SASO_WARPS * NS * HALVES * 16 + (size_t) c * HALVES * 4;
         if (nst * sb <= SMEM_MAX && (int64_t) ck <= ((K + 63) & ~(int64_t) 63)) { CK = ck; cap = c; stage = sb; break; }

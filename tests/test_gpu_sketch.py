@@ -233,6 +233,23 @@ def test_saso_medium(rb, cuda, dt):
         run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 2048, 64, 4096, 1.0, 0.0, 8, "S", key=7)
 
 
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_saso_tail_paths(rb, cuda, dt, monkeypatch):
+    """The streaming SASO kernel's three homes of an entry: the slot record (first three per row and chunk), the staged
+    tail region, and -- when a bucket's tails do not fit the region -- global memory. RBX_SASO_CAP shrinks the region so
+    that the last path runs; vec_nnz = 32 on a short operator makes every row's tail long."""
+    cases = [("L", "C", 256, 96, 16384, 8), ("L", "R", 200, 40, 5000, 8), ("L", "R", 64, 48, 2048, 32), ("L", "C", 2048, 32, 4096, 8),
+             ("L", "R", 130, 17, 777, 19)]
+    for cap in (None, "0", "32", "96"):
+        if cap is None:
+            monkeypatch.delenv("RBX_SASO_CAP", raising=False)
+        else:
+            monkeypatch.setenv("RBX_SASO_CAP", cap)
+        for side, layout, d, n, m, k in cases:
+            run_sparseop_case(rb, cuda, dt, side, layout, "N", "N", d, n, m, 1.5, 0.0, k, "S", key=3)
+    monkeypatch.delenv("RBX_SASO_CAP", raising=False)
+
+
 # ---------------------------------------------------------------------------------------------- sparse data
 def random_sparse(rng, rows, cols, density, npdt):
     M = rng.standard_normal((rows, cols)) * (rng.random((rows, cols)) < density)
