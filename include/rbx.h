@@ -41,6 +41,9 @@ int rbx_free(void* dev_ptr);
 int rbx_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* stream);
 int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream);
 int rbx_stream_synchronize(void* stream);
+/* Kernel workspaces (operator codes, split partials, operator slabs) come from the device's default stream-ordered pool and
+   stay mapped between calls; this synchronises the device and returns them to the driver. */
+int rbx_trim_workspace(void);
 
 /* ---- RNG state algebra (host-side, exact) ------------------------------------------------------ */
 /* ctr += n with carry: Random123 array.h incr(); pinned by test/test_basic_rng/test_r123.cc:679-766 */

@@ -357,8 +357,8 @@ static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p
     if (alpha == (T) 0) return RBX_OK;
     const size_t nnz = (size_t)(vec_nnz * (major_axis == 'S' ? lng : sht));
     int64_t *rows = nullptr, *cols = nullptr; T* vals = nullptr;
-    if (cudaMallocAsync(&rows, nnz * 8, st) != cudaSuccess || cudaMallocAsync(&cols, nnz * 8, st) != cudaSuccess ||
-        cudaMallocAsync(&vals, nnz * sizeof(T), st) != cudaSuccess) {
+    if (ws_alloc(&rows, nnz * 8, st) != cudaSuccess || ws_alloc(&cols, nnz * 8, st) != cudaSuccess ||
+        ws_alloc(&vals, nnz * sizeof(T), st) != cudaSuccess) {
         cudaGetLastError();
         if (rows) cudaFreeAsync(rows, st);
         if (cols) cudaFreeAsync(cols, st);
@@ -404,7 +404,7 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
     const int64_t *prow = idx0, *pcol = idx1;
     int64_t* expanded = nullptr;
     if (fmt != 'O') {
-        if (cudaMallocAsync(&expanded, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+        if (ws_alloc(&expanded, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
         int rc = (fmt == 'R') ? launch_expand_ptr(A_rows, idx0, expanded, st) : launch_expand_ptr(A_cols, idx1, expanded, st);
         if (rc != RBX_OK) { cudaFreeAsync(expanded, st); return rc; }
         if (fmt == 'R') { prow = expanded; pcol = idx1; } else { prow = idx0; pcol = expanded; }
@@ -418,7 +418,7 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
     if (Ks < 1) Ks = 1;
     if (Ks > s.K) Ks = s.K;
     T* Sd = nullptr;
-    if (cudaMallocAsync(&Sd, sizeof(T) * (size_t)(s.M * Ks), st) != cudaSuccess) {
+    if (ws_alloc(&Sd, sizeof(T) * (size_t)(s.M * Ks), st) != cudaSuccess) {
         cudaGetLastError();
         if (expanded) cudaFreeAsync(expanded, st);
         return RBX_ERR_ALLOC;
@@ -611,6 +611,12 @@ int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* st
     return cudaMemcpyAsync(dst_host, src_dev, (size_t) bytes, cudaMemcpyDeviceToHost, (cudaStream_t) stream) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;
 }
 int rbx_stream_synchronize(void* stream) { return cudaStreamSynchronize((cudaStream_t) stream) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA; }
+int rbx_trim_workspace(void) {
+    int dev = 0;
+    cudaMemPool_t pool;
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetDefaultMemPool(&pool, dev) != cudaSuccess) return RBX_ERR_CUDA;
+    return cudaMemPoolTrimTo(pool, 0) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;
+}
 
 int rbx_host_fill_sparse_f64_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
                                  int64_t* rows_host, int64_t* cols_host, double* vals_host, uint32_t next_ctr[4]) {

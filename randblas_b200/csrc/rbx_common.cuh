@@ -18,6 +18,27 @@ inline int check_launch(const char* what) {
     }
     return RBX_OK;
 }
+// Stream-ordered workspace from the device's default memory pool. The pool's release threshold is raised once per device
+// so that a workspace freed by one call is still mapped for the next (the default threshold of 0 hands the memory back to
+// the driver at every synchronisation: re-mapping a few hundred MB costs more than the kernels here).
+// rbx_trim_workspace() gives it back.
+inline cudaError_t ws_alloc(void** p, size_t bytes, cudaStream_t stream) {
+    static bool raised[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && !raised[dev]) {
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        raised[dev] = true;
+    }
+    return cudaMallocAsync(p, bytes, stream);
+}
+template <typename P> inline cudaError_t ws_alloc(P** p, size_t bytes, cudaStream_t stream) {
+    return ws_alloc(reinterpret_cast<void**>(p), bytes, stream);
+}
+
 #define RBX_CUDA_TRY(expr)                                                                   \
     do {                                                                                     \
         cudaError_t e__ = (expr);                                                            \

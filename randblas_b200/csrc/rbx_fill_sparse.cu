@@ -75,7 +75,7 @@ int launch_fisher_yates(const Ctr128& ctr, const Key64& key, int64_t vec_nnz, in
     }
     int64_t ctas = dim_minor < kNumSMs * 4 ? dim_minor : kNumSMs * 4;
     int64_t* scratch = nullptr;
-    if (cudaMallocAsync(&scratch, sizeof(int64_t) * (size_t)(ctas * (dim_major + vec_nnz)), stream) != cudaSuccess) {
+    if (ws_alloc(&scratch, sizeof(int64_t) * (size_t)(ctas * (dim_major + vec_nnz)), stream) != cudaSuccess) {
         cudaGetLastError();
         return RBX_ERR_ALLOC;
     }

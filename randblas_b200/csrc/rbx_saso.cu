@@ -524,10 +524,10 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     uint32_t* codes = nullptr; uint32_t* rec = nullptr; uint32_t* ws = nullptr; T* partial = nullptr;
     const size_t Np = (size_t) njb * W;
     const size_t part_bytes = msplit > 1 ? (size_t) msplit * M * Np * sizeof(T) : 0;
-    if (cudaMallocAsync(&codes, (size_t) nchunks * stream_stride * 4, stream) != cudaSuccess ||
-        cudaMallocAsync(&rec, (size_t) nchunks * rec_stride * 4, stream) != cudaSuccess ||
-        cudaMallocAsync(&ws, (size_t) nchunks * ws_stride * 4, stream) != cudaSuccess ||
-        (part_bytes && cudaMallocAsync(&partial, part_bytes, stream) != cudaSuccess)) {
+    if (ws_alloc(&codes, (size_t) nchunks * stream_stride * 4, stream) != cudaSuccess ||
+        ws_alloc(&rec, (size_t) nchunks * rec_stride * 4, stream) != cudaSuccess ||
+        ws_alloc(&ws, (size_t) nchunks * ws_stride * 4, stream) != cudaSuccess ||
+        (part_bytes && ws_alloc(&partial, part_bytes, stream) != cudaSuccess)) {
         cudaGetLastError();
         if (codes) cudaFreeAsync(codes, stream);
         if (rec) cudaFreeAsync(rec, stream);

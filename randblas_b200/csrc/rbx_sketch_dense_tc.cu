@@ -329,7 +329,7 @@ int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream
     a.dbg = getenv("RBX_TC_DBG") ? atoi(getenv("RBX_TC_DBG")) : 0;
     a.Mpad = (g.M + 31) & ~(int64_t) 31; a.Npad = g.N;
     a.partial = nullptr;
-    if (ksplit > 1 && cudaMallocAsync(&a.partial, sizeof(float) * (size_t) ksplit * a.Mpad * a.Npad, stream) != cudaSuccess) {
+    if (ksplit > 1 && ws_alloc(&a.partial, sizeof(float) * (size_t) ksplit * a.Mpad * a.Npad, stream) != cudaSuccess) {
         cudaGetLastError();
         return RBX_ERR_ALLOC;
     }
