@@ -335,9 +335,11 @@ int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream
     }
     auto kern = g.w.family == 'G' ? sketch_dense_tc_kernel<'G'> : sketch_dense_tc_kernel<'U'>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) TC_SMEM);
-    // Cluster sharing of the generated operator tile works (parity-tested with RBX_TC_CLUSTER=2/4) but measured slower and
-    // erratic on B200 (lock-step coupling of the CTAs + cluster wave quantisation), so it is opt-in for now.
-    a.cl = 1;
+    // Pairs of CTAs that are neighbours along n form a cluster: each generates half of the operator tile and multicasts it
+    // (st.async + tcgen05.commit.multicast), which halves the FP64-bound generation per output. Measured on C1: Gaussian
+    // 1.74 -> 1.31 ms, uniform 0.76 -> 0.71 ms; clusters of 4 lose more to lock-step coupling than they save (1.92 ms).
+    // Generating several K blocks per pass for more independent FP64 chains per thread was tried and gained < 5 %.
+    a.cl = (a.tiles_n % 2 == 0) ? 2 : 1;
     if (const char* ev = getenv("RBX_TC_CLUSTER")) { const int v = atoi(ev); if ((v == 1 || v == 2 || v == 4) && a.tiles_n % v == 0) a.cl = v; }
     {
         cudaLaunchConfig_t cfg = {};
