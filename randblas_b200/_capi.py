@@ -9,7 +9,8 @@ import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 HEADER = os.path.join(os.path.dirname(_HERE), "include", "rbx.h")
-LIBPATH = os.path.join(_HERE, "librbx.so")
+# RBX_LIBRARY: another build of the same library (kernel experiments); the default is the in-tree one
+LIBPATH = os.environ.get("RBX_LIBRARY") or os.path.join(_HERE, "librbx.so")
 
 _CT = {
     "void": None, "char": ctypes.c_char, "int": ctypes.c_int, "int64_t": ctypes.c_int64, "uint64_t": ctypes.c_uint64,

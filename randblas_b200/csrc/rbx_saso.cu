@@ -39,7 +39,16 @@ constexpr int SASO_R = SASO_WARPS * SASO_RW;   // rows of B per CTA
 constexpr int SASO_THREADS = SASO_WARPS * 32;
 // ring stages: row-contiguous data runs two long chunks (compute per chunk far exceeds the copy latency, and a longer
 // chunk means more entries per accumulator slot); the slower element-wise copy of column-contiguous data wants three
-constexpr int SASO_NST_ROWS = 2, SASO_NST_COLS = 3;
+#ifndef SASO_NST_COLS_VAL
+#define SASO_NST_COLS_VAL 2
+#endif
+#ifndef SASO_CK_MAX
+#define SASO_CK_MAX 704         // longest chunk (a multiple of 64); the ring stages must fit in shared memory
+#endif
+#ifndef SASO_ALWAYS
+#define SASO_ALWAYS 1         // leading gathers of a slot that are not predicated (a row has a first entry 86 % of the time at C2)
+#endif
+constexpr int SASO_NST_ROWS = 2, SASO_NST_COLS = SASO_NST_COLS_VAL;
 constexpr uint32_t SASO_SIGN = 0x80000000u;
 #ifndef SASO_NU_VAL
 #define SASO_NU_VAL 3
@@ -115,15 +124,15 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     for (int r = t; r < Mp; r += SASO_THREADS) rowcnt[r] = 0;
     for (int e = t; e < E; e += SASO_THREADS) trow[e] = 0xFFFF;
     __syncthreads();
-    const int64_t l = chunk * CK + t;
-    if (t < CK && l < K) {
-        const uint32_t c = (uint32_t) t;
-        const uint32_t base = c * pitch_el;
+    for (int cc = t; cc < CK; cc += SASO_THREADS) {
+        const int64_t l = chunk * CK + cc;
+        if (l >= K) break;
+        const uint32_t base = (uint32_t) cc * pitch_el;
         fy_vector<KMAX>(ctr, key, co + l, vec_nnz, dim_major, [&](int j, int64_t idx, bool negative) {
             const int64_t r = idx - ro;
             if (r >= 0 && r < M) {
-                tcode[t * vec_nnz + j] = base | (negative ? SASO_SIGN : 0u);
-                trow[t * vec_nnz + j] = (uint16_t) r;
+                tcode[cc * vec_nnz + j] = base | (negative ? SASO_SIGN : 0u);
+                trow[cc * vec_nnz + j] = (uint16_t) r;
                 atomicAdd(&rowcnt[r], 1u);
             }
         });
@@ -289,7 +298,14 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, const 
 #pragma unroll
         for (int k = 0; k < SASO_NU; ++k)
 #pragma unroll
-            for (int j = 0; j < G; ++j) v[j][k] = lds_raw_nz<T>(lanebase + (c[j][k] << SH), c[j][k], zero_code);
+            for (int j = 0; j < G; ++j) {
+                if (k < SASO_ALWAYS) {
+                    if (sizeof(T) == 8) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(*reinterpret_cast<unsigned long long*>(&v[j][k])) : "r"(lanebase + (c[j][k] << SH)));
+                    else asm volatile("ld.shared.b32 %0, [%1];" : "=r"(*reinterpret_cast<uint32_t*>(&v[j][k])) : "r"(lanebase + (c[j][k] << SH)));
+                } else {
+                    v[j][k] = lds_raw_nz<T>(lanebase + (c[j][k] << SH), c[j][k], zero_code);
+                }
+            }
 #pragma unroll
         for (int k = 0; k < SASO_NU; ++k)
 #pragma unroll
@@ -378,19 +394,21 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
                     cp_async16(st + p * 16, src, (uint32_t) nb);
                 }
             }
-        } else if (tid < CK) {
-            const int64_t l = (int64_t) ch * CK + tid;
-            const uint32_t row = st + tid * PITCH;
-            if (inside) {
-                const T* src = a.X + l + j0 * a.sx_j;
+        } else {
+            for (int rr = tid; rr < CK; rr += SASO_THREADS) {
+                const int64_t l = (int64_t) ch * CK + rr;
+                const uint32_t row = st + rr * PITCH;
+                if (inside) {
+                    const T* src = a.X + l + j0 * a.sx_j;
 #pragma unroll
-                for (int jj = 0; jj < W; ++jj) { cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), src, (uint32_t) sizeof(T)); src += a.sx_j; }
-            } else {
-                const T* src = a.X + (l < a.K ? l : 0) + j0 * a.sx_j;
+                    for (int jj = 0; jj < W; ++jj) { cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), src, (uint32_t) sizeof(T)); src += a.sx_j; }
+                } else {
+                    const T* src = a.X + (l < a.K ? l : 0) + j0 * a.sx_j;
 #pragma unroll 4
-                for (int jj = 0; jj < W; ++jj) {
-                    const uint32_t nb = (l < a.K && j0 + jj < a.N) ? (uint32_t) sizeof(T) : 0u;
-                    cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), nb ? src + jj * a.sx_j : a.X, nb);
+                    for (int jj = 0; jj < W; ++jj) {
+                        const uint32_t nb = (l < a.K && j0 + jj < a.N) ? (uint32_t) sizeof(T) : 0u;
+                        cp_async_small<(int) sizeof(T)>(row + jj * (int) sizeof(T), nb ? src + jj * a.sx_j : a.X, nb);
+                    }
                 }
             }
         }
@@ -496,7 +514,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     int CK = 0, cap = 0;
     const size_t nst = cols_contig ? SASO_NST_COLS : SASO_NST_ROWS;
     size_t stage = 0;
-    for (int ck = 512; ck >= 64; ck -= (cols_contig ? 16 : 64)) {
+    for (int ck = SASO_CK_MAX; ck >= 64; ck -= (cols_contig ? 16 : 64)) {
+        if ((size_t) ck * vec_nnz * 10 + (size_t)(2 * nbuckets * SASO_RW + 3 * nbuckets * NS + 2) * 4 + 16 > SMEM_MAX) continue;   // the prep kernel's sort
         // tail elements of one row block per chunk: mean + 8 sigma (Poisson tails; sigma^2 < 2 * mean); a bucket that
         // does not fit reads its tails from global memory
         const double lambda = (double) ck * (double) vec_nnz / (double) S_rows;
