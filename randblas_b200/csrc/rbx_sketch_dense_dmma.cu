@@ -1,0 +1,209 @@
+// K2 (double precision, the C5 case): panelled generate-and-contract on the FP64 tensor cores.
+//
+// Replaces dense::lskge3 / dense::rskge3 for T = double (skge.hh:173-215, 320-364: materialise submat(S), blas::gemm).
+// The FP64 pipe is the bound here (DMMA.8x8x4 is the only FP64 tensor instruction sm_100a has: measured 37.1 TFLOP/s
+// register-resident, cuBLAS DGEMM 35.5), and the bit-exact Box-Muller also runs on that pipe (~50 FP64 operations per
+// sample). Generating the operator tile inside every CTA would repeat that work N / 128 times (39 % extra FP64 work at
+// a 128-wide tile), so the operator is generated ONCE per k-panel into a fixed-size, L2-resident workspace
+// (M x Kp doubles, <= 32 MB whatever d * m is) by K1 and contracted by the DMMA kernel below, panel after panel with
+// beta = 1. Nothing proportional to d * m is allocated; generation is ~1 % of the FP64 work.
+//
+// dmma_gemm_kernel: C (M x N) = alpha * Sp (M x Kp, k contiguous) * X (Kp x N) + beta * C.
+//   CTA tile 128 x 128 x 16, 8 warps as 2 (M) x 4 (N), warp tile 64 x 32 = 8 x 4 DMMA.8x8x4 fragments (64 accumulators
+//   per thread). Operands come through a 4-stage cp.async ring (16-byte chunks, zero-fill for ragged edges); rows are
+//   padded so that the 8-byte fragment loads of a half-warp hit 16 distinct bank pairs.
+#include "rbx_kernels.cuh"
+#include <cstdlib>
+
+namespace rbx {
+
+constexpr int DM_BM = 128, DM_BN = 128, DM_BK = 16, DM_STAGES = 4, DM_THREADS = 256;
+constexpr int DM_PITCH_K = DM_BK + 4;        // k-contiguous tile: 128 rows x 20 doubles (row shift 32 B mod 128 B)
+constexpr int DM_PITCH_J = DM_BN + 4;        // j-contiguous data tile: 16 rows x 132 doubles
+constexpr int DM_TILE_DOUBLES = DM_BM * DM_PITCH_K;                 // 2560 doubles = 20480 B (>= 16 * 132)
+constexpr size_t DM_SMEM = (size_t) DM_STAGES * 2 * DM_TILE_DOUBLES * sizeof(double);   // 163840 B
+
+struct DmmaArgs {
+    const double* S; int64_t s_pitch;        // operator panel, S[i * s_pitch + l]
+    const double* X; int64_t sx_l, sx_j;     // data, X[l * sx_l + j * sx_j]; one of the strides is 1
+    double* C; int64_t sc_i, sc_j;
+    int64_t M, N, K;                         // K = panel length
+    double alpha, beta;
+    int tiles_n;
+};
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ int clamp_bytes(int64_t elems) {
+    return elems >= 2 ? 16 : (elems == 1 ? 8 : 0);
+}
+
+// XJ = false: X is k-contiguous (sx_l == 1; column-major data, NoTrans). XJ = true: X is j-contiguous (sx_j == 1).
+template <bool XJ>
+__global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs a) {
+    extern __shared__ __align__(16) double dm_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp >> 2, wn = warp & 3;                 // 2 x 4 warps
+    const int g = lane >> 2, t = lane & 3;
+    const int64_t i0 = ((int64_t) blockIdx.x / a.tiles_n) * DM_BM, j0 = ((int64_t) blockIdx.x % a.tiles_n) * DM_BN;
+    const uint32_t smem_base = (uint32_t) __cvta_generic_to_shared(dm_smem);
+    const int nk = (int)((a.K + DM_BK - 1) / DM_BK);
+
+    auto load_stage = [&](int kt, int slot) {
+        const int64_t k0 = (int64_t) kt * DM_BK;
+        const uint32_t sS = smem_base + (uint32_t)(slot * 2 * DM_TILE_DOUBLES) * 8u;
+        const uint32_t sX = sS + (uint32_t) DM_TILE_DOUBLES * 8u;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
+            const int64_t gi = i0 + row;
+            const bool ok = gi < a.M;
+            const double* src = a.S + (ok ? gi : 0) * a.s_pitch + (k0 + kc < a.K ? k0 + kc : 0);
+            cp_async16(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(a.K - k0 - kc) : 0);
+        }
+        if (!XJ) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
+                const int64_t gj = j0 + row;
+                const bool ok = gj < a.N;
+                const double* src = a.X + (ok ? gj : 0) * a.sx_j + (k0 + kc < a.K ? k0 + kc : 0);
+                cp_async16(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(a.K - k0 - kc) : 0);
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = tid + q * DM_THREADS, l = c >> 6, jc = (c & 63) * 2;
+                const int64_t gl = k0 + l;
+                const bool ok = gl < a.K;
+                const double* src = a.X + (ok ? gl : 0) * a.sx_l + (j0 + jc < a.N ? j0 + jc : 0);
+                cp_async16(sX + (uint32_t)(l * DM_PITCH_J + jc) * 8u, src, ok ? clamp_bytes(a.N - j0 - jc) : 0);
+            }
+        }
+    };
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int f = 0; f < 8; ++f)
+#pragma unroll
+        for (int h = 0; h < 4; ++h) { acc[f][h][0] = 0.0; acc[f][h][1] = 0.0; }
+
+#pragma unroll
+    for (int s = 0; s < DM_STAGES - 1; ++s) {
+        if (s < nk) load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nk; ++kt) {
+        cp_async_wait<DM_STAGES - 2>();
+        __syncthreads();
+        if (kt + DM_STAGES - 1 < nk) load_stage(kt + DM_STAGES - 1, (kt + DM_STAGES - 1) % DM_STAGES);
+        cp_async_commit();
+        const double* Ss = dm_smem + (size_t)(kt % DM_STAGES) * 2 * DM_TILE_DOUBLES;
+        const double* Xs = Ss + DM_TILE_DOUBLES;
+        const double* pa = Ss + (wm * 64 + g) * DM_PITCH_K + t;
+        const double* pb = XJ ? Xs + t * DM_PITCH_J + wn * 32 + g : Xs + (wn * 32 + g) * DM_PITCH_K + t;
+#pragma unroll
+        for (int kk = 0; kk < DM_BK / 4; ++kk) {
+            double fa[8], fb[4];
+#pragma unroll
+            for (int f = 0; f < 8; ++f) fa[f] = pa[f * 8 * DM_PITCH_K + kk * 4];
+#pragma unroll
+            for (int h = 0; h < 4; ++h) fb[h] = XJ ? pb[kk * 4 * DM_PITCH_J + h * 8] : pb[h * 8 * DM_PITCH_K + kk * 4];
+#pragma unroll
+            for (int f = 0; f < 8; ++f)
+#pragma unroll
+                for (int h = 0; h < 4; ++h) dmma884(acc[f][h][0], acc[f][h][1], fa[f], fb[h]);
+        }
+    }
+    cp_async_wait<0>();
+
+    // epilogue: lane (g, t) holds C[row g][cols 2t, 2t + 1] of each 8 x 8 fragment
+#pragma unroll
+    for (int f = 0; f < 8; ++f) {
+        const int64_t gi = i0 + wm * 64 + f * 8 + g;
+        if (gi >= a.M) continue;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int64_t gj = j0 + wn * 32 + h * 8 + 2 * t + e;
+                if (gj < a.N) {
+                    double* c = a.C + gi * a.sc_i + gj * a.sc_j;
+                    const double v = a.alpha * acc[f][h][e];
+                    *c = (a.beta == 0.0) ? v : v + a.beta * (*c);     // beta == 0: C is not read (BLAS convention)
+                }
+            }
+        }
+    }
+}
+
+static int launch_dmma_gemm(const DmmaArgs& a_in, cudaStream_t stream) {
+    DmmaArgs a = a_in;
+    a.tiles_n = (int)((a.N + DM_BN - 1) / DM_BN);
+    const int64_t tiles = (int64_t) a.tiles_n * ((a.M + DM_BM - 1) / DM_BM);
+    if (tiles > 0x7fffffffll) return RBX_ERR_UNSUPPORTED;
+    const bool xj = (a.sx_l != 1);
+    auto kern = xj ? dmma_gemm_kernel<true> : dmma_gemm_kernel<false>;
+    static bool attr_set[2] = { false, false };
+    if (!attr_set[xj]) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) DM_SMEM) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_CUDA; }
+        attr_set[xj] = true;
+    }
+    kern<<<(unsigned) tiles, DM_THREADS, DM_SMEM, stream>>>(a);
+    count_launch();
+    return check_launch("dmma_gemm_kernel");
+}
+
+int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
+    if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 64 || g.N < 64 || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
+    if (!((g.sx_l == 1 && g.sx_j % 2 == 0) || (g.sx_j == 1 && g.sx_l % 2 == 0))) return RBX_ERR_UNSUPPORTED;
+    if (g.Sx && (g.ss_l != 1 || g.ss_i % 2 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0)) return RBX_ERR_UNSUPPORTED;
+    if (g.alpha == 0.0) return launch_scale_view<double>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
+
+    DmmaArgs a;
+    a.X = g.X; a.sx_l = g.sx_l; a.sx_j = g.sx_j;
+    a.C = g.C; a.sc_i = g.sc_i; a.sc_j = g.sc_j;
+    a.M = g.M; a.N = g.N; a.alpha = g.alpha; a.tiles_n = 0;
+    if (g.Sx) {                                   // DenseSkOp::buff given: one pass over the caller's array
+        a.S = g.Sx; a.s_pitch = g.ss_i; a.K = g.K; a.beta = g.beta;
+        return launch_dmma_gemm(a, stream);
+    }
+    // implicit operator: k-panels of a fixed-size workspace (<= 32 MB, stays in the 126 MB L2 together with the X panel)
+    int64_t kp = ((int64_t) 32 << 20) / (8 * g.M);
+    if (const char* ev = getenv("RBX_DMMA_PANEL")) { const int64_t v = atoll(ev); if (v >= 16) kp = v; }
+    kp = (kp / 16) * 16;
+    if (kp < 64) kp = 64;
+    if (kp > g.K) kp = (g.K + 15) / 16 * 16;
+    double* panel = nullptr;
+    if (ws_alloc(&panel, sizeof(double) * (size_t) g.M * (size_t) kp, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    int rc = RBX_OK;
+    for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kp) {
+        const int64_t kl = (l0 + kp <= g.K) ? kp : g.K - l0;
+        if (g.l_on_cols)   // parent rows = i, parent columns = l: counters run along the panel's contiguous axis
+            rc = launch_fill_window<double>(g.w.family, g.w.W * 4, panel, g.M, kl, g.w.pr0, g.w.pc0 + l0, g.w.ctr, g.w.key,
+                                            kp, 1, g.w.family == 'U', stream);
+        else               // parent rows = l, parent columns = i
+            rc = launch_fill_window<double>(g.w.family, g.w.W * 4, panel, kl, g.M, g.w.pr0 + l0, g.w.pc0, g.w.ctr, g.w.key,
+                                            1, kp, g.w.family == 'U', stream);
+        if (rc != RBX_OK) break;
+        a.S = panel; a.s_pitch = kp; a.K = kl;
+        a.X = g.X + l0 * g.sx_l;
+        a.beta = (l0 == 0) ? g.beta : 1.0;
+        rc = launch_dmma_gemm(a, stream);
+    }
+    cudaFreeAsync(panel, stream);
+    return rc;
+}
+
+}  // namespace rbx

@@ -363,6 +363,4 @@ int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream
     return rc;
 }
 
-int launch_sketch_dense_tc_f64(const GemmOperands<double>&, cudaStream_t) { return RBX_ERR_UNSUPPORTED; }
-
 }  // namespace rbx

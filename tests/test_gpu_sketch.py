@@ -144,6 +144,39 @@ def test_sketch_general_dense_tensor_core_path(rb, cuda):
         assert ratio < 0.05      # 3xTF32 with FP32 accumulation sits far inside the FP32 GEMM bound
 
 
+def test_sketch_general_dense_dmma_path(rb, cuda, monkeypatch):
+    """double problems inside the DMMA kernel's envelope (rbx_sketch_dense_dmma.cu): ragged M / N / K (odd K included),
+    operator offsets, alpha / beta, both families and major axes, both data layouts, the right-sketch form, a pre-filled
+    operator, and several k-panels (RBX_DMMA_PANEL shrinks the panel). Launches = panels x (operator panel fill + DMMA
+    GEMM); the SIMT kernel would be 1."""
+    cases = [("L", "C", "N", "N", 200, 260, 4100, 1.0, 0.0, (0, 0), "G", "L", 0, 1),
+             ("L", "C", "N", "N", 200, 260, 4101, 1.5, -0.5, (5, 8), "G", "L", 1, 5),
+             ("L", "R", "N", "N", 130, 260, 4100, 1.0, 0.0, (0, 3), "U", "L", 0, 5),
+             ("L", "C", "N", "N", 128, 512, 2052, 1.0, 0.5, (2, 1), "G", "S", 0, 3),
+             ("R", "R", "N", "N", 256, 300, 4100, 1.0, 2.0, (0, 0), "G", "L", 0, 1),
+             ("L", "R", "N", "T", 256, 256, 4096, 1.0, 0.0, (0, 0), "U", "L", 0, 4)]
+    for (side, layout, opS, opA, d, n, m, alpha, beta, off, fam, ma, lda_pad, panels) in cases:
+        if panels > 1:
+            monkeypatch.setenv("RBX_DMMA_PANEL", "1024")
+        else:
+            monkeypatch.delenv("RBX_DMMA_PANEL", raising=False)
+        l0 = rb.lib.rbx_launch_count()
+        ro, co = off
+        if side == "R":
+            ratio = run_dense_case(rb, cuda, "f64", side, layout, opS, opA, d, m, n, alpha, beta, off=(co, ro), D_extra=(8, 3), fam=fam, ma=ma)
+        else:
+            ratio = run_dense_case(rb, cuda, "f64", side, layout, opS, opA, d, n, m, alpha, beta, off=(ro, co), D_extra=(3, 8), fam=fam, ma=ma,
+                                   lda_pad=lda_pad)
+        launches = rb.lib.rbx_launch_count() - l0
+        assert launches == 2 * panels, f"expected {panels} panel(s) of fill + DMMA GEMM, saw {launches} launch(es) for {(side, layout, d, n, m)}"
+        assert ratio < 0.05
+    monkeypatch.delenv("RBX_DMMA_PANEL", raising=False)
+    # DenseSkOp::buff given (explicit operator, k contiguous): one DMMA launch, no fill
+    l0 = rb.lib.rbx_launch_count()
+    run_dense_case(rb, cuda, "f64", "L", "C", "N", "N", 192, 256, 4096, 1.0, 0.5, prefilled=True)
+    assert rb.lib.rbx_launch_count() - l0 == 2      # fill_dense(S) + DMMA GEMM
+
+
 def test_nan_in_B_is_overwritten_when_beta_is_zero(rb, cuda):
     """util::safe_scal (util.hh:51-59) / BLAS convention: beta == 0 never reads B"""
     S = rb.DenseSkOp(rb.DenseDist(4, 9), 1)
