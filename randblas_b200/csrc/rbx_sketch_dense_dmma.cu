@@ -5,7 +5,7 @@
 // register-resident, cuBLAS DGEMM 35.5), and the bit-exact Box-Muller also runs on that pipe (~50 FP64 operations per
 // sample). Generating the operator tile inside every CTA would repeat that work N / 128 times (39 % extra FP64 work at
 // a 128-wide tile), so the operator is generated ONCE per k-panel into a fixed-size, L2-resident workspace
-// (M x Kp doubles, <= 32 MB whatever d * m is) by K1 and contracted by the DMMA kernel below, panel after panel with
+// (M x Kp doubles, <= 256 MB whatever d * m is) by K1 and contracted by the DMMA kernel below, panel after panel with
 // beta = 1. Nothing proportional to d * m is allocated; generation is ~1 % of the FP64 work.
 //
 // dmma_gemm_kernel: C (M x N) = alpha * Sp (M x Kp, k contiguous) * X (Kp x N) + beta * C.
@@ -48,7 +48,7 @@ __device__ __forceinline__ int clamp_bytes(int64_t elems) {
 }
 
 // XJ = false: X is k-contiguous (sx_l == 1; column-major data, NoTrans). XJ = true: X is j-contiguous (sx_j == 1).
-template <bool XJ>
+template <bool XJ, bool CI>
 __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs a) {
     extern __shared__ __align__(16) double dm_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -126,23 +126,54 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
     }
     cp_async_wait<0>();
 
-    // epilogue: lane (g, t) holds C[row g][cols 2t, 2t + 1] of each 8 x 8 fragment
+    // epilogue: lane (g, t) holds C[row g][cols 2t, 2t + 1] of each 8 x 8 fragment. The tile goes through shared memory
+    // (the ring is free now) so that global traffic runs along C's unit-stride axis in 256-byte warp rows, with the
+    // old values of four rows in flight per thread when beta != 0.
+    __syncthreads();
+    constexpr int P = CI ? 130 : 136;            // staging pitch: conflict-free for the fragment stores below
+    if (CI) {                                     // C is i-contiguous (ColMajor B): stage as Cs[j][i]
 #pragma unroll
-    for (int f = 0; f < 8; ++f) {
-        const int64_t gi = i0 + wm * 64 + f * 8 + g;
-        if (gi >= a.M) continue;
+        for (int f = 0; f < 8; ++f)
 #pragma unroll
-        for (int h = 0; h < 4; ++h) {
+            for (int h = 0; h < 4; ++h)
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int64_t gj = j0 + wn * 32 + h * 8 + 2 * t + e;
-                if (gj < a.N) {
-                    double* c = a.C + gi * a.sc_i + gj * a.sc_j;
-                    const double v = a.alpha * acc[f][h][e];
-                    *c = (a.beta == 0.0) ? v : v + a.beta * (*c);     // beta == 0: C is not read (BLAS convention)
+                for (int e = 0; e < 2; ++e)
+                    dm_smem[(wn * 32 + h * 8 + 2 * t + e) * P + wm * 64 + f * 8 + g] = acc[f][h][e];
+    } else {                                      // C is j-contiguous: stage as Cs[i][j], two columns per 16-byte store
+#pragma unroll
+        for (int f = 0; f < 8; ++f)
+#pragma unroll
+            for (int h = 0; h < 4; ++h)
+                *reinterpret_cast<double2*>(&dm_smem[(wm * 64 + f * 8 + g) * P + wn * 32 + h * 8 + 2 * t]) =
+                    make_double2(acc[f][h][0], acc[f][h][1]);
+    }
+    __syncthreads();
+    // "line" = index along the slow axis of C, "pos" = index along its unit-stride axis
+    const int64_t line0 = CI ? j0 : i0, pos0 = CI ? i0 : j0;
+    const int64_t nline = CI ? a.N : a.M, npos = CI ? a.M : a.N;
+    const int64_t s_line = CI ? a.sc_j : a.sc_i;
+#pragma unroll 1
+    for (int lb = warp * 16; lb < warp * 16 + 16; lb += 4) {
+        double old[4][4];
+        if (a.beta != 0.0) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int64_t gl = line0 + lb + u, gp = pos0 + lane + 32 * q;
+                    old[u][q] = (gl < nline && gp < npos) ? a.C[gl * s_line + gp] : 0.0;
+                }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int64_t gl = line0 + lb + u, gp = pos0 + lane + 32 * q;
+                if (gl < nline && gp < npos) {
+                    const double v = a.alpha * dm_smem[(lb + u) * P + lane + 32 * q];
+                    a.C[gl * s_line + gp] = (a.beta == 0.0) ? v : v + a.beta * old[u][q];   // beta == 0: C is not read
                 }
             }
-        }
     }
 }
 
@@ -151,12 +182,14 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, cudaStream_t stream) {
     a.tiles_n = (int)((a.N + DM_BN - 1) / DM_BN);
     const int64_t tiles = (int64_t) a.tiles_n * ((a.M + DM_BM - 1) / DM_BM);
     if (tiles > 0x7fffffffll) return RBX_ERR_UNSUPPORTED;
-    const bool xj = (a.sx_l != 1);
-    auto kern = xj ? dmma_gemm_kernel<true> : dmma_gemm_kernel<false>;
-    static bool attr_set[2] = { false, false };
-    if (!attr_set[xj]) {
+    const bool xj = (a.sx_l != 1), ci = (a.sc_i == 1);
+    auto kern = xj ? (ci ? dmma_gemm_kernel<true, true> : dmma_gemm_kernel<true, false>)
+                   : (ci ? dmma_gemm_kernel<false, true> : dmma_gemm_kernel<false, false>);
+    static bool attr_set[4] = { false, false, false, false };
+    const int which = (xj ? 2 : 0) + (ci ? 1 : 0);
+    if (!attr_set[which]) {
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) DM_SMEM) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_CUDA; }
-        attr_set[xj] = true;
+        attr_set[which] = true;
     }
     kern<<<(unsigned) tiles, DM_THREADS, DM_SMEM, stream>>>(a);
     count_launch();
@@ -169,6 +202,7 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
     if (reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
     if (!((g.sx_l == 1 && g.sx_j % 2 == 0) || (g.sx_j == 1 && g.sx_l % 2 == 0))) return RBX_ERR_UNSUPPORTED;
     if (g.Sx && (g.ss_l != 1 || g.ss_i % 2 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0)) return RBX_ERR_UNSUPPORTED;
+    if (g.sc_i != 1 && g.sc_j != 1) return RBX_ERR_UNSUPPORTED;
     if (g.alpha == 0.0) return launch_scale_view<double>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
 
     DmmaArgs a;
@@ -179,8 +213,9 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
         a.S = g.Sx; a.s_pitch = g.ss_i; a.K = g.K; a.beta = g.beta;
         return launch_dmma_gemm(a, stream);
     }
-    // implicit operator: k-panels of a fixed-size workspace (<= 32 MB, stays in the 126 MB L2 together with the X panel)
-    int64_t kp = ((int64_t) 32 << 20) / (8 * g.M);
+    // implicit operator: k-panels of a fixed-size workspace (<= 256 MB; the CTAs of one row of tiles run together and share
+    // their operator rows through L2). Longer panels amortise the read-modify-write of C between panels.
+    int64_t kp = ((int64_t) 256 << 20) / (8 * g.M);
     if (const char* ev = getenv("RBX_DMMA_PANEL")) { const int64_t v = atoll(ev); if (v >= 16) kp = v; }
     kp = (kp / 16) * 16;
     if (kp < 64) kp = 64;

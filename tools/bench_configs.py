@@ -60,8 +60,8 @@ def main():
             ms = timeit(lambda: rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A, m, 0.0, B, d), args.reps)
             tf = 2.0 * d * n * m / ms / 1e9
             emit({"config": "C1", "family": fam, "ms": ms, "tflops": tf, "flops": 2.0 * d * n * m,
-                  "roofline": {"bound": "tensor", "peak_note": "3xTF32: useful peak = TF32 dense / 3; TF32 dense taken as bf16_tflops / 2 from MEASURED_PEAKS.json",
-                               "peak_tflops": float(peaks["bf16_tflops"]) / 2 / 3, "frac": tf / (float(peaks["bf16_tflops"]) / 2 / 3)},
+                  "roofline": {"bound": "tensor", "peak_note": "3xTF32: useful peak = TF32 dense / 3; TF32 dense = cuBLAS TF32 GEMM 8192^3 measured on this pool (746.4 TFLOP/s, tools/micro/cublas_peaks.py)",
+                               "peak_tflops": 746.4 / 3, "frac": tf / (746.4 / 3)},
                   "kernel": "sketch_dense_tc_kernel (tcgen05) + tc_reduce_kernel"})
         del A, B
 
@@ -106,8 +106,8 @@ def main():
         ms = timeit(lambda: rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A, m, 1.0, B, d), max(2, args.reps // 2))
         tf = 2.0 * d * n * m / ms / 1e9
         emit({"config": "C5", "slab_rows": m, "full_rows": 1 << 23, "ms_slab": ms, "tflops": tf, "extrapolated_full_s": ms * ((1 << 23) / m) / 1e3,
-              "roofline": {"bound": "fp64", "peak_tflops": 40.0, "peak_note": "nominal B200 FP64 (not in MEASURED_PEAKS.json)", "frac": tf / 40.0},
-              "kernel": "sketch_dense_simt_kernel<double>"})
+              "roofline": {"bound": "fp64", "peak_tflops": 37.1, "peak_note": "DMMA.8x8x4 register-resident issue rate measured on this pool's B200 (tools/micro/fp64_peak.cu; cuBLAS DGEMM 8192^3 = 35.5)", "frac": tf / 37.1},
+              "kernel": "fill_dense_kernel (operator k-panels) + dmma_gemm_kernel"})
     return out
 
 
