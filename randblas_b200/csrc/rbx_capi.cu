@@ -397,45 +397,54 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
     const bool l_on_cols = ((!s.s_trans) == (w.parent_is_S != 0));
     RBX_NEED_DEVICE();
     cudaStream_t st = (cudaStream_t) stream;
-    RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));
-    if (alpha == (T) 0 || nnz == 0 || s.M == 0 || s.N == 0 || s.K == 0) return RBX_OK;
+    if (alpha == (T) 0 || nnz == 0 || s.M == 0 || s.N == 0 || s.K == 0)
+        return launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st);
 
-    // per-nonzero (row, col) of the sparse matrix
-    const int64_t *prow = idx0, *pcol = idx1;
-    int64_t* expanded = nullptr;
-    if (fmt != 'O') {
-        if (ws_alloc(&expanded, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
-        int rc = (fmt == 'R') ? launch_expand_ptr(A_rows, idx0, expanded, st) : launch_expand_ptr(A_cols, idx1, expanded, st);
-        if (rc != RBX_OK) { cudaFreeAsync(expanded, st); return rc; }
-        if (fmt == 'R') { prow = expanded; pcol = idx1; } else { prow = idx0; pcol = expanded; }
-    }
     // entry (p, q) of A sits at (l, j) of op(A) for the left sketch when opA == 'N'; the right sketch is
     // transposed, so there (p, q) -> (j, l) when opA == 'N'.
     const bool a_trans = (side == 'L') ? (opA == 'T') : (opA == 'N');
-    // the operator window is generated in slabs of the contraction axis, M x Ks at a time (i contiguous)
+    // column segments of op(A): CSC NoTrans and CSR Trans are grouped by j already (whole matrix, offsets 0);
+    // everything else is regrouped on the device (rbx_spdata.cu)
+    const int64_t *seg_ptr = nullptr, *seg_l = nullptr; const T* seg_v = nullptr;
+    int64_t *own_ptr = nullptr, *own_l = nullptr, *expanded = nullptr; T* own_v = nullptr;
+    int rc = RBX_OK;
+    if (fmt == 'C' && !a_trans)      { seg_ptr = idx1; seg_l = idx0; seg_v = vals; }
+    else if (fmt == 'R' && a_trans)  { seg_ptr = idx0; seg_l = idx1; seg_v = vals; }
+    else {
+        const int64_t *prow = idx0, *pcol = idx1;
+        if (fmt != 'O') {
+            if (ws_alloc(&expanded, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+            rc = (fmt == 'R') ? launch_expand_ptr(A_rows, idx0, expanded, st) : launch_expand_ptr(A_cols, idx1, expanded, st);
+            if (fmt == 'R') { prow = expanded; pcol = idx1; } else { prow = idx0; pcol = expanded; }
+        }
+        if (rc == RBX_OK) rc = spd_group_by_column<T>(nnz, prow, pcol, vals, a_trans, ro_a, co_a, s.K, s.N, &own_ptr, &own_l, &own_v, st);
+        if (expanded) cudaFreeAsync(expanded, st);
+        if (rc != RBX_OK) return rc;
+        seg_ptr = own_ptr; seg_l = own_l; seg_v = own_v;
+    }
+    // the operator window is generated in slabs of the contraction axis, as floats, Mp x Ks at a time (i contiguous)
+    const int64_t Mp = (s.M + 3) & ~(int64_t) 3;
     const int64_t budget = (int64_t) 4 << 30;
-    int64_t Ks = budget / ((int64_t) sizeof(T) * s.M);
+    int64_t Ks = budget / (4 * Mp);
+    if (const char* ev = getenv("RBX_SPD_SLAB")) { const int64_t v = atoll(ev); if (v >= 1) Ks = v; }
     if (Ks < 1) Ks = 1;
     if (Ks > s.K) Ks = s.K;
-    T* Sd = nullptr;
-    if (ws_alloc(&Sd, sizeof(T) * (size_t)(s.M * Ks), st) != cudaSuccess) {
-        cudaGetLastError();
-        if (expanded) cudaFreeAsync(expanded, st);
-        return RBX_ERR_ALLOC;
-    }
+    float* Sd = nullptr;
+    if (ws_alloc(&Sd, 4 * (size_t)(Mp * Ks), st) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
     const int64_t ma = major_axis_length(D_rows, D_cols, major_axis);
-    int rc = RBX_OK;
     for (int64_t l0 = 0; l0 < s.K && rc == RBX_OK; l0 += Ks) {
         const int64_t kk = (s.K - l0 < Ks) ? s.K - l0 : Ks;
-        if (l_on_cols) rc = launch_fill_window<T>(family, ma, Sd, s.M, kk, w.pr0, w.pc0 + l0, w.ctr, w.key, 1, s.M, family == 'U', st);
-        else           rc = launch_fill_window<T>(family, ma, Sd, kk, s.M, w.pr0 + l0, w.pc0, w.ctr, w.key, s.M, 1, family == 'U', st);
+        // unscaled floats: the uniform family's sqrt(3) is applied in T precision by the gather kernel
+        if (l_on_cols) rc = launch_fill_window<float>(family, ma, Sd, s.M, kk, w.pr0, w.pc0 + l0, w.ctr, w.key, 1, Mp, false, st);
+        else           rc = launch_fill_window<float>(family, ma, Sd, kk, s.M, w.pr0 + l0, w.pc0, w.ctr, w.key, Mp, 1, false, st);
         if (rc != RBX_OK) break;
-        // shift the sparse offsets so that l is measured from the slab start
-        const int64_t ro = a_trans ? ro_a : ro_a + l0, co = a_trans ? co_a + l0 : co_a;
-        rc = launch_spdata_scatter<T>(nnz, prow, pcol, vals, a_trans, ro, co, s.M, s.N, kk, alpha, Sd, B, s.sc_i, s.sc_j, st);
+        rc = launch_spdata_gather<T>(s.N, seg_ptr, seg_l, seg_v, l0, kk, s.M, Mp, Sd, family == 'U', l0 == 0, alpha, beta, B,
+                                     s.sc_i, s.sc_j, st);
     }
-    cudaFreeAsync(Sd, st);
-    if (expanded) cudaFreeAsync(expanded, st);
+    if (Sd) cudaFreeAsync(Sd, st);
+    if (own_ptr) cudaFreeAsync(own_ptr, st);
+    if (own_l) cudaFreeAsync(own_l, st);
+    if (own_v) cudaFreeAsync(own_v, st);
     return rc;
 }
 

@@ -55,6 +55,17 @@ template <typename T>
 int launch_spdata_scatter(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
                           int64_t M, int64_t N, int64_t K, T alpha, const T* Sd, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
 
+// K5 (rbx_spdata.cu): output-stationary gather. Column j of C gets alpha * sum over the entries (l, v) of segment j of
+// v * Sd[(l - l0) * Mp + i]; `first` applies beta (C not read when beta == 0), later slabs accumulate.
+template <typename T>
+int launch_spdata_gather(int64_t N, const int64_t* ptr, const int64_t* lidx, const T* vals, int64_t l0, int64_t kk, int64_t M, int64_t Mp,
+                         const float* Sd, bool uniform, bool first, T alpha, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+// regroup per-nonzero (p, q, v) into column segments of op(A) (sorted by l inside a segment). The three outputs are
+// stream-ordered allocations the caller releases with cudaFreeAsync.
+template <typename T>
+int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
+                        int64_t K, int64_t N, int64_t** ptr_out, int64_t** lidx_out, T** vals_out, cudaStream_t stream);
+
 // expand a CSR rowptr / CSC colptr (n_outer + 1 entries) into one outer index per nonzero
 int launch_expand_ptr(int64_t n_outer, const int64_t* ptr, int64_t* outer_idx, cudaStream_t stream);
 

@@ -361,6 +361,28 @@ def test_sketch_sparse(rb, cuda, dt, fmt):
             rb.sketch_sparse(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 5, 9, 20, 1.0, S, 0, 0, A, 0, 1, 0.0, B, 5)
 
 
+@pytest.mark.parametrize("fmt", ["O", "R", "C"])
+def test_sketch_sparse_medium_slabs_and_determinism(rb, cuda, fmt, monkeypatch):
+    """rbx_spdata.cu at sizes that use several 512-row chunks of the operator (M = 601: padded pitch), several warps per
+    column pass and several contraction slabs (RBX_SPD_SLAB); the regrouped formats must give bitwise identical results
+    from run to run (the column segments are rank-sorted after the atomic scatter)."""
+    run_sparsedata_case(rb, cuda, "f64", "L", "C", "N", "N", 601, 300, 700, 1.5, -0.5, fmt, 0.05, off_s=(1, 2))
+    run_sparsedata_case(rb, cuda, "f32", "R", "R", "N", "N", 130, 400, 500, 1.0, 0.0, fmt, 0.1, fam="U")
+    monkeypatch.setenv("RBX_SPD_SLAB", "97")
+    run_sparsedata_case(rb, cuda, "f64", "L", "C", "N", "N", 601, 300, 700, 1.5, -0.5, fmt, 0.05, off_s=(1, 2))
+    run_sparsedata_case(rb, cuda, "f64", "L", "R", "T", "T", 64, 300, 700, 1.0, 2.0, fmt, 0.05, ma="S")
+    monkeypatch.delenv("RBX_SPD_SLAB", raising=False)
+    rng = np.random.default_rng(5)
+    A = to_fmt(rb, cuda, random_sparse(rng, 2000, 1500, 0.02, np.float64), fmt)
+    S = rb.DenseSkOp(rb.DenseDist(96, 2000), 3, dtype=torch.float64)
+    outs = []
+    for _ in range(3):
+        B = torch.zeros(96 * 1500, dtype=torch.float64, device=cuda)
+        rb.sketch_sparse(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 96, 1500, 2000, 1.0, S, 0, 0, A, 0, 0, 0.0, B, 96)
+        outs.append(B.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
 # ---------------------------------------------------------------------------------------------- wrappers
 @pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_sketch_vector(rb, cuda, dt):

@@ -94,7 +94,7 @@ def main():
         byts = nnz * 16.0 + (n + 1) * 8.0 + d * n * 8.0
         emit({"config": "C4", "n": n, "full_config_n": 1000000, "nnz": nnz, "d": d, "ms": ms, "gflops": 2.0 * d * nnz / ms / 1e6,
               "roofline": {"bound": "hbm", "algorithmic_bytes": byts, "achieved_gbs": byts / ms / 1e6, "peak_gbs": hbm, "frac": byts / ms / 1e6 / hbm},
-              "kernel": "fill_dense_kernel (operator slab) + spdata_scatter_kernel"})
+              "kernel": "spd_group_by_column (CSR -> column segments) + fill_dense_kernel (float operator slab) + spdata_gather_kernel"})
         del A, B, vals, cols
 
     if not only or "C5" in only:
