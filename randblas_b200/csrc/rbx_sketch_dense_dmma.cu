@@ -48,13 +48,16 @@ __device__ __forceinline__ int clamp_bytes(int64_t elems) {
 }
 
 // XJ = false: X is k-contiguous (sx_l == 1; column-major data, NoTrans). XJ = true: X is j-contiguous (sx_j == 1).
-template <bool XJ, bool CI>
+// MF = 8-row fragments per warp along M: the CTA tile is (16 * MF) x 128. The launcher picks MF in {8, 7, 6} (tile heights
+// 128 / 112 / 96) so that the number of CTAs fills whole waves of the 148 SMs.
+template <bool XJ, bool CI, int MF>
 __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs a) {
+    constexpr int BM = 16 * MF;
     extern __shared__ __align__(16) double dm_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp >> 2, wn = warp & 3;                 // 2 x 4 warps
     const int g = lane >> 2, t = lane & 3;
-    const int64_t i0 = ((int64_t) blockIdx.x / a.tiles_n) * DM_BM, j0 = ((int64_t) blockIdx.x % a.tiles_n) * DM_BN;
+    const int64_t i0 = ((int64_t) blockIdx.x / a.tiles_n) * BM, j0 = ((int64_t) blockIdx.x % a.tiles_n) * DM_BN;
     const uint32_t smem_base = (uint32_t) __cvta_generic_to_shared(dm_smem);
     const int nk = (int)((a.K + DM_BK - 1) / DM_BK);
 
@@ -63,8 +66,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         const uint32_t sS = smem_base + (uint32_t)(slot * 2 * DM_TILE_DOUBLES) * 8u;
         const uint32_t sX = sS + (uint32_t) DM_TILE_DOUBLES * 8u;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < (BM * 8 + DM_THREADS - 1) / DM_THREADS; ++q) {
             const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
+            if (BM * 8 % DM_THREADS != 0 && row >= BM) break;
             const int64_t gi = i0 + row;
             const bool ok = gi < a.M;
             const double* src = a.S + (ok ? gi : 0) * a.s_pitch + (k0 + kc < a.K ? k0 + kc : 0);
@@ -91,9 +95,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         }
     };
 
-    double acc[8][4][2];
+    double acc[MF][4][2];
 #pragma unroll
-    for (int f = 0; f < 8; ++f)
+    for (int f = 0; f < MF; ++f)
 #pragma unroll
         for (int h = 0; h < 4; ++h) { acc[f][h][0] = 0.0; acc[f][h][1] = 0.0; }
 
@@ -109,17 +113,17 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         cp_async_commit();
         const double* Ss = dm_smem + (size_t)(kt % DM_STAGES) * 2 * DM_TILE_DOUBLES;
         const double* Xs = Ss + DM_TILE_DOUBLES;
-        const double* pa = Ss + (wm * 64 + g) * DM_PITCH_K + t;
+        const double* pa = Ss + (wm * (8 * MF) + g) * DM_PITCH_K + t;
         const double* pb = XJ ? Xs + t * DM_PITCH_J + wn * 32 + g : Xs + (wn * 32 + g) * DM_PITCH_K + t;
 #pragma unroll
         for (int kk = 0; kk < DM_BK / 4; ++kk) {
-            double fa[8], fb[4];
+            double fa[MF], fb[4];
 #pragma unroll
-            for (int f = 0; f < 8; ++f) fa[f] = pa[f * 8 * DM_PITCH_K + kk * 4];
+            for (int f = 0; f < MF; ++f) fa[f] = pa[f * 8 * DM_PITCH_K + kk * 4];
 #pragma unroll
             for (int h = 0; h < 4; ++h) fb[h] = XJ ? pb[kk * 4 * DM_PITCH_J + h * 8] : pb[h * 8 * DM_PITCH_K + kk * 4];
 #pragma unroll
-            for (int f = 0; f < 8; ++f)
+            for (int f = 0; f < MF; ++f)
 #pragma unroll
                 for (int h = 0; h < 4; ++h) dmma884(acc[f][h][0], acc[f][h][1], fa[f], fb[h]);
         }
@@ -133,18 +137,18 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
     constexpr int P = CI ? 130 : 136;            // staging pitch: conflict-free for the fragment stores below
     if (CI) {                                     // C is i-contiguous (ColMajor B): stage as Cs[j][i]
 #pragma unroll
-        for (int f = 0; f < 8; ++f)
+        for (int f = 0; f < MF; ++f)
 #pragma unroll
             for (int h = 0; h < 4; ++h)
 #pragma unroll
                 for (int e = 0; e < 2; ++e)
-                    dm_smem[(wn * 32 + h * 8 + 2 * t + e) * P + wm * 64 + f * 8 + g] = acc[f][h][e];
+                    dm_smem[(wn * 32 + h * 8 + 2 * t + e) * P + wm * (8 * MF) + f * 8 + g] = acc[f][h][e];
     } else {                                      // C is j-contiguous: stage as Cs[i][j], two columns per 16-byte store
 #pragma unroll
-        for (int f = 0; f < 8; ++f)
+        for (int f = 0; f < MF; ++f)
 #pragma unroll
             for (int h = 0; h < 4; ++h)
-                *reinterpret_cast<double2*>(&dm_smem[(wm * 64 + f * 8 + g) * P + wn * 32 + h * 8 + 2 * t]) =
+                *reinterpret_cast<double2*>(&dm_smem[(wm * (8 * MF) + f * 8 + g) * P + wn * 32 + h * 8 + 2 * t]) =
                     make_double2(acc[f][h][0], acc[f][h][1]);
     }
     __syncthreads();
@@ -161,7 +165,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int64_t gl = line0 + lb + u, gp = pos0 + lane + 32 * q;
-                    old[u][q] = (gl < nline && gp < npos) ? a.C[gl * s_line + gp] : 0.0;
+                    const bool in_tile = CI ? (lane + 32 * q < BM) : (lb + u < BM);
+                    old[u][q] = (in_tile && gl < nline && gp < npos) ? a.C[gl * s_line + gp] : 0.0;
                 }
         }
 #pragma unroll
@@ -169,7 +174,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int64_t gl = line0 + lb + u, gp = pos0 + lane + 32 * q;
-                if (gl < nline && gp < npos) {
+                const bool in_tile = CI ? (lane + 32 * q < BM) : (lb + u < BM);
+                if (in_tile && gl < nline && gp < npos) {
                     const double v = a.alpha * dm_smem[(lb + u) * P + lane + 32 * q];
                     a.C[gl * s_line + gp] = (a.beta == 0.0) ? v : v + a.beta * old[u][q];   // beta == 0: C is not read
                 }
@@ -177,14 +183,11 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
     }
 }
 
-static int launch_dmma_gemm(const DmmaArgs& a_in, cudaStream_t stream) {
-    DmmaArgs a = a_in;
-    a.tiles_n = (int)((a.N + DM_BN - 1) / DM_BN);
-    const int64_t tiles = (int64_t) a.tiles_n * ((a.M + DM_BM - 1) / DM_BM);
-    if (tiles > 0x7fffffffll) return RBX_ERR_UNSUPPORTED;
+template <int MF>
+static int launch_dmma_gemm_mf(const DmmaArgs& a, int64_t tiles, cudaStream_t stream) {
     const bool xj = (a.sx_l != 1), ci = (a.sc_i == 1);
-    auto kern = xj ? (ci ? dmma_gemm_kernel<true, true> : dmma_gemm_kernel<true, false>)
-                   : (ci ? dmma_gemm_kernel<false, true> : dmma_gemm_kernel<false, false>);
+    auto kern = xj ? (ci ? dmma_gemm_kernel<true, true, MF> : dmma_gemm_kernel<true, false, MF>)
+                   : (ci ? dmma_gemm_kernel<false, true, MF> : dmma_gemm_kernel<false, false, MF>);
     static bool attr_set[4] = { false, false, false, false };
     const int which = (xj ? 2 : 0) + (ci ? 1 : 0);
     if (!attr_set[which]) {
@@ -194,6 +197,37 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, cudaStream_t stream) {
     kern<<<(unsigned) tiles, DM_THREADS, DM_SMEM, stream>>>(a);
     count_launch();
     return check_launch("dmma_gemm_kernel");
+}
+
+// tile height for this shape: the one whose CTA count wastes the least of its last wave (cost = waves x tile height)
+static int pick_mf(int64_t M, int64_t N) {
+    if (const char* ev = getenv("RBX_DMMA_MF")) { const int v = atoi(ev); if (v >= 6 && v <= 8) return v; }
+    const int64_t tn = (N + DM_BN - 1) / DM_BN;
+    int best = 8; int64_t best_cost = -1;
+    for (int mf = 8; mf >= 6; --mf) {
+        const int64_t tiles = tn * ((M + 16 * mf - 1) / (16 * mf));
+        const int64_t cost = ((tiles + kNumSMs - 1) / kNumSMs) * mf;
+        if (best_cost < 0 || cost < best_cost) { best = mf; best_cost = cost; }
+    }
+    return best;
+}
+
+static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
+    DmmaArgs a = a_in;
+    a.tiles_n = (int)((a.N + DM_BN - 1) / DM_BN);
+    const int64_t tiles = (int64_t) a.tiles_n * ((a.M + 16 * mf - 1) / (16 * mf));
+    if (tiles > 0x7fffffffll) return RBX_ERR_UNSUPPORTED;
+    return mf == 8 ? launch_dmma_gemm_mf<8>(a, tiles, stream) : mf == 7 ? launch_dmma_gemm_mf<7>(a, tiles, stream)
+                                                                      : launch_dmma_gemm_mf<6>(a, tiles, stream);
+}
+
+// one auxiliary (non-blocking) stream per device for the panel generator
+static cudaStream_t dmma_aux_stream() {
+    static cudaStream_t aux[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!aux[dev] && cudaStreamCreateWithFlags(&aux[dev], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return aux[dev];
 }
 
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
@@ -211,7 +245,7 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
     a.M = g.M; a.N = g.N; a.alpha = g.alpha; a.tiles_n = 0;
     if (g.Sx) {                                   // DenseSkOp::buff given: one pass over the caller's array
         a.S = g.Sx; a.s_pitch = g.ss_i; a.K = g.K; a.beta = g.beta;
-        return launch_dmma_gemm(a, stream);
+        return launch_dmma_gemm(a, pick_mf(g.M, g.N), stream);
     }
     // implicit operator: k-panels of a fixed-size workspace (<= 256 MB; the CTAs of one row of tiles run together and share
     // their operator rows through L2). Longer panels amortise the read-modify-write of C between panels.
@@ -220,22 +254,53 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
     kp = (kp / 16) * 16;
     if (kp < 64) kp = 64;
     if (kp > g.K) kp = (g.K + 15) / 16 * 16;
+    const int mf = pick_mf(g.M, g.N);
+    // Two panel buffers when there is more than one panel: panel p + 1 is generated on an auxiliary stream while the GEMM
+    // of panel p runs (the generator is issue-bound, the GEMM DMMA-bound; without the overlap the fill is ~9 % of the time
+    // of a 512-column shard). Events order buffer reuse; the caller's stream waits for every fill, so freeing on it is safe.
+    const int64_t npanels = (g.K + kp - 1) / kp;
+    const int nbuf = (npanels > 1 && !getenv("RBX_DMMA_NO_OVERLAP")) ? 2 : 1;
+    const size_t panel_elems = (size_t) g.M * (size_t) kp;
     double* panel = nullptr;
-    if (ws_alloc(&panel, sizeof(double) * (size_t) g.M * (size_t) kp, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    if (ws_alloc(&panel, sizeof(double) * panel_elems * nbuf, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    cudaStream_t aux = stream;
+    cudaEvent_t ready = nullptr, filled[2] = { nullptr, nullptr }, used[2] = { nullptr, nullptr };
     int rc = RBX_OK;
-    for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kp) {
+    if (nbuf == 2) {
+        aux = dmma_aux_stream();
+        bool ok = aux != nullptr && cudaEventCreateWithFlags(&ready, cudaEventDisableTiming) == cudaSuccess;
+        for (int b = 0; b < 2 && ok; ++b)
+            ok = cudaEventCreateWithFlags(&filled[b], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&used[b], cudaEventDisableTiming) == cudaSuccess;
+        ok = ok && cudaEventRecord(ready, stream) == cudaSuccess && cudaStreamWaitEvent(aux, ready, 0) == cudaSuccess;
+        if (!ok) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    }
+    int64_t p = 0;
+    for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kp, ++p) {
         const int64_t kl = (l0 + kp <= g.K) ? kp : g.K - l0;
+        const int b = (nbuf == 2) ? (int)(p & 1) : 0;
+        double* buf = panel + (size_t) b * panel_elems;
+        if (nbuf == 2 && p >= 2 && cudaStreamWaitEvent(aux, used[b], 0) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; break; }
         if (g.l_on_cols)   // parent rows = i, parent columns = l: counters run along the panel's contiguous axis
-            rc = launch_fill_window<double>(g.w.family, g.w.W * 4, panel, g.M, kl, g.w.pr0, g.w.pc0 + l0, g.w.ctr, g.w.key,
-                                            kp, 1, g.w.family == 'U', stream);
+            rc = launch_fill_window<double>(g.w.family, g.w.W * 4, buf, g.M, kl, g.w.pr0, g.w.pc0 + l0, g.w.ctr, g.w.key,
+                                            kp, 1, g.w.family == 'U', aux);
         else               // parent rows = l, parent columns = i
-            rc = launch_fill_window<double>(g.w.family, g.w.W * 4, panel, kl, g.M, g.w.pr0 + l0, g.w.pc0, g.w.ctr, g.w.key,
-                                            1, kp, g.w.family == 'U', stream);
+            rc = launch_fill_window<double>(g.w.family, g.w.W * 4, buf, kl, g.M, g.w.pr0 + l0, g.w.pc0, g.w.ctr, g.w.key,
+                                            1, kp, g.w.family == 'U', aux);
         if (rc != RBX_OK) break;
-        a.S = panel; a.s_pitch = kp; a.K = kl;
+        if (nbuf == 2 && (cudaEventRecord(filled[b], aux) != cudaSuccess || cudaStreamWaitEvent(stream, filled[b], 0) != cudaSuccess)) {
+            cudaGetLastError(); rc = RBX_ERR_CUDA; break;
+        }
+        a.S = buf; a.s_pitch = kp; a.K = kl;
         a.X = g.X + l0 * g.sx_l;
         a.beta = (l0 == 0) ? g.beta : 1.0;
-        rc = launch_dmma_gemm(a, stream);
+        rc = launch_dmma_gemm(a, mf, stream);
+        if (rc == RBX_OK && nbuf == 2 && cudaEventRecord(used[b], stream) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    }
+    if (nbuf == 2) {
+        if (rc != RBX_OK) cudaStreamSynchronize(aux);      // error path: nothing may still be writing the panels
+        if (ready) cudaEventDestroy(ready);
+        for (int b = 0; b < 2; ++b) { if (filled[b]) cudaEventDestroy(filled[b]); if (used[b]) cudaEventDestroy(used[b]); }
     }
     cudaFreeAsync(panel, stream);
     return rc;
