@@ -53,23 +53,30 @@ __global__ void __launch_bounds__(256) fill_dense_kernel(T* __restrict__ out, co
     int64_t i, b;
     if (p.rows_fastest) { b = tid / p.n_srows; i = tid - b * p.n_srows; }
     else                { i = tid / p.nblk;    b = tid - i * p.nblk; }
+    // running counter offset and output pointer, advanced by the (rows, blocks) stride with one wrap correction
+    uint64_t coff = (uint64_t)((p.r0 + i) * p.W + p.blk0 + b);
+    T* dst = out + i * p.rs + ((p.blk0 + b) * 4 - p.c0) * p.cs;
+    const uint64_t coff_step = (uint64_t)(p.step_i * p.W + p.step_b);
+    const int64_t dst_step = p.step_i * p.rs + p.step_b * 4 * p.cs;
+    const uint64_t coff_wrap = p.rows_fastest ? (uint64_t)(1 - p.n_srows * p.W) : (uint64_t)(p.W - p.nblk);
+    const int64_t dst_wrap = p.rows_fastest ? 4 * p.cs - p.n_srows * p.rs : p.rs - p.nblk * 4 * p.cs;
     for (int64_t it = tid; it < p.items; it += (int64_t) gridDim.x * blockDim.x) {
-        const Ctr128 c = ctr_add(p.ctr, (uint64_t)((p.r0 + i) * p.W + p.blk0 + b));
+        const Ctr128 c = ctr_add(p.ctr, coff);
         const float4 v = generate4<FAMILY>(philox4x32_10(c, p.key), tab);
-        const int64_t j0 = (p.blk0 + b) * 4 - p.c0;     // window column of lane 0 (may be negative)
-        T* dst = out + i * p.rs + j0 * p.cs;
         const T e0 = cast_scale<T>(v.x, scale, do_scale), e1 = cast_scale<T>(v.y, scale, do_scale),
                 e2 = cast_scale<T>(v.z, scale, do_scale), e3 = cast_scale<T>(v.w, scale, do_scale);
         if (VEC) {
             store4<T>(dst, e0, e1, e2, e3);
         } else {
+            const int64_t j0 = (p.blk0 + b) * 4 - p.c0;     // window column of lane 0 (may be negative)
             if (j0 >= 0 && j0 < p.n_scols)         dst[0] = e0;
             if (j0 + 1 >= 0 && j0 + 1 < p.n_scols) dst[p.cs] = e1;
             if (j0 + 2 >= 0 && j0 + 2 < p.n_scols) dst[2 * p.cs] = e2;
             if (j0 + 3 >= 0 && j0 + 3 < p.n_scols) dst[3 * p.cs] = e3;
         }
-        if (p.rows_fastest) { i += p.step_i; b += p.step_b; if (i >= p.n_srows) { i -= p.n_srows; b += 1; } }
-        else                { b += p.step_b; i += p.step_i; if (b >= p.nblk)    { b -= p.nblk;    i += 1; } }
+        coff += coff_step; dst += dst_step;
+        if (p.rows_fastest) { i += p.step_i; b += p.step_b; if (i >= p.n_srows) { i -= p.n_srows; b += 1; coff += coff_wrap; dst += dst_wrap; } }
+        else                { b += p.step_b; i += p.step_i; if (b >= p.nblk)    { b -= p.nblk;    i += 1; coff += coff_wrap; dst += dst_wrap; } }
     }
 }
 
