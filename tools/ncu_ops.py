@@ -14,7 +14,7 @@ for r in rows[hi + 1:]:
     op = [o for o in r[c["Source"]].strip().split() if not o.startswith("@")][0].split('.')[0]
     e = int(r[c["Instructions Executed"]]); s = int(r[c["# Samples"]])
     ex[op] += e; smp[op] += s; tot += s; totex += e
-    wf[op] += int(r[c["L1 Wavefronts Shared"]] or 0)
+    wf[op] += int(r[c["L1 Wavefronts Shared"]] or 0) if "L1 Wavefronts Shared" in c else 0
     for k in stalls:
         stall[k] += int(r[c[k]] or 0)
 print("total executed warp-instr", totex, "samples", tot)
