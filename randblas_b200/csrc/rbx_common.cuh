@@ -39,6 +39,15 @@ template <typename P> inline cudaError_t ws_alloc(P** p, size_t bytes, cudaStrea
     return ws_alloc(reinterpret_cast<void**>(p), bytes, stream);
 }
 
+// one auxiliary (non-blocking) stream per device: operator panels are generated on it while the previous panel's GEMM runs
+inline cudaStream_t aux_stream() {
+    static cudaStream_t aux[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!aux[dev] && cudaStreamCreateWithFlags(&aux[dev], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return aux[dev];
+}
+
 #define RBX_CUDA_TRY(expr)                                                                   \
     do {                                                                                     \
         cudaError_t e__ = (expr);                                                            \

@@ -221,15 +221,6 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
                                                                       : launch_dmma_gemm_mf<6>(a, tiles, stream);
 }
 
-// one auxiliary (non-blocking) stream per device for the panel generator
-static cudaStream_t dmma_aux_stream() {
-    static cudaStream_t aux[64] = {};
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    if (!aux[dev] && cudaStreamCreateWithFlags(&aux[dev], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-    return aux[dev];
-}
-
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
     if (g.M < 64 || g.N < 64 || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
@@ -267,7 +258,7 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
     cudaEvent_t ready = nullptr, filled[2] = { nullptr, nullptr }, used[2] = { nullptr, nullptr };
     int rc = RBX_OK;
     if (nbuf == 2) {
-        aux = dmma_aux_stream();
+        aux = aux_stream();
         bool ok = aux != nullptr && cudaEventCreateWithFlags(&ready, cudaEventDisableTiming) == cudaSuccess;
         for (int b = 0; b < 2 && ok; ++b)
             ok = cudaEventCreateWithFlags(&filled[b], cudaEventDisableTiming) == cudaSuccess &&

@@ -108,6 +108,7 @@ struct TcArgs {
     float* partial;               // [ksplit][Npad][Mpad] when ksplit > 1
     int64_t Mpad, Npad;
     int nk, ksplit, tiles_n, dbg, cl;
+    const float* Sx; int64_t s_pitch;   // FAMILY 'X': operator values read from a k-contiguous array (panel workspace or S.buff)
 };
 
 template <char FAMILY>
@@ -200,12 +201,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (e < my_chunks && i0 + r < a.M && l0 + 4 * c < a.K) {
-                    const Ctr128 ctr = ctr_add(a.w.ctr, (uint64_t)((a.w.pr0 + i0 + r) * a.w.W + cbase + c));
-                    v = generate4<FAMILY>(philox4x32_10(ctr, a.w.key), tab);
+                    if (FAMILY == 'X') {
+                        v = __ldg(reinterpret_cast<const float4*>(a.Sx + (i0 + r) * a.s_pitch + l0 + 4 * c));
+                    } else {
+                        const Ctr128 ctr = ctr_add(a.w.ctr, (uint64_t)((a.w.pr0 + i0 + r) * a.w.W + cbase + c));
+                        v = generate4<FAMILY>(philox4x32_10(ctr, a.w.key), tab);
+                    }
                     if (FAMILY == 'U') { v.x = __fmul_rn(v.x, scale); v.y = __fmul_rn(v.y, scale); v.z = __fmul_rn(v.z, scale); v.w = __fmul_rn(v.w, scale); }
-                    if (l0 + 4 * c + 1 >= a.K) v.y = 0.f;
-                    if (l0 + 4 * c + 2 >= a.K) v.z = 0.f;
-                    if (l0 + 4 * c + 3 >= a.K) v.w = 0.f;
+                    if (FAMILY != 'X') {           // 'X': masked where the values are consumed, so the load stays in flight
+                        if (l0 + 4 * c + 1 >= a.K) v.y = 0.f;
+                        if (l0 + 4 * c + 2 >= a.K) v.z = 0.f;
+                        if (l0 + 4 * c + 3 >= a.K) v.w = 0.f;
+                    }
                 }
                 vals[q] = v;
             }
@@ -221,7 +228,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 const int e = gt + q * TC_GEN_WARPS * 32;
                 if (e < my_chunks) {
                     const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
-                    const float4 v = vals[q];
+                    float4 v = vals[q];
+                    if (FAMILY == 'X') {
+                        const int64_t lc = (int64_t)(kb + it) * TC_BK + 4 * c;
+                        if (lc + 1 >= a.K) v.y = 0.f;
+                        if (lc + 2 >= a.K) v.z = 0.f;
+                        if (lc + 3 >= a.K) v.w = 0.f;
+                    }
                     float4 hi, lo;
                     hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
                     hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
@@ -239,6 +252,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 for (int p = 0; p < a.cl; ++p)
                     asm volatile("mbarrier.complete_tx.relaxed.cluster.shared::cluster.b64 [%0], %1;" :: "r"(mapa_u32(bar_u32, (uint32_t) p)), "r"(2 * TC_S_BYTES / a.cl) : "memory");
             }
+            // operator values read from memory: issue the loads of the next stage now, so that their latency is covered by
+            // the X split below (the generated families compute theirs after handing the stage over instead)
+            if (FAMILY == 'X' && it + 1 < nit) generate(it + 1);
             mbar_wait(&full_x[xs], (it / TC_XST) & 1);
             float4* xh = reinterpret_cast<float4*>(smem + (size_t) xs * TC_X_BYTES);
             float4* xl = reinterpret_cast<float4*>(smem + TC_OFF_XLO + (size_t) s * TC_X_BYTES);
@@ -255,7 +271,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
             fence_proxy_async();                           // generic-proxy writes -> visible to the tensor core (async proxy)
             __syncwarp();
             if (lane == 0) mbar_arrive(&ready_x[s]);
-            if (it + 1 < nit) generate(it + 1);
+            if (FAMILY != 'X' && it + 1 < nit) generate(it + 1);
         }
         // ---- epilogue: TMEM -> registers -> global ----
         mbar_wait(&done, 0);
@@ -302,20 +318,16 @@ __global__ void __launch_bounds__(256) tc_reduce_kernel(const float* __restrict_
     }
 }
 
-int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
-    if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.Sx != nullptr || !g.l_on_cols || (g.w.pc0 & 3) != 0) return RBX_ERR_UNSUPPORTED;
-    if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 64 || g.N < 64 || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
-    if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;
-    if (g.alpha == 0.f) return launch_scale_view<float>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
-
+// one launch of the tensor-core kernel (+ split-K reduce). mode: 'G' / 'U' = operator generated in the kernel from g.w;
+// 'X' = operator values read from Sx[i * s_pitch + l].
+static int tc_launch(const GemmOperands<float>& g, char mode, const float* Sx, int64_t s_pitch, cudaStream_t stream) {
     CUtensorMap tmap;
     if (!make_tmap_2d(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, g.X, (uint64_t) g.K, (uint64_t) g.N, (uint64_t) g.sx_j * 4, TC_BK, TC_BN,
                       CU_TENSOR_MAP_SWIZZLE_128B))
         return RBX_ERR_UNSUPPORTED;
 
     TcArgs a;
+    a.Sx = Sx; a.s_pitch = s_pitch;
     a.w = g.w; a.M = g.M; a.N = g.N; a.K = g.K; a.alpha = g.alpha; a.beta = g.beta; a.C = g.C; a.sc_i = g.sc_i; a.sc_j = g.sc_j;
     const int tiles_m = (int)((g.M + TC_BM - 1) / TC_BM);
     a.tiles_n = (int)((g.N + TC_BN - 1) / TC_BN);
@@ -333,7 +345,7 @@ int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream
         cudaGetLastError();
         return RBX_ERR_ALLOC;
     }
-    auto kern = g.w.family == 'G' ? sketch_dense_tc_kernel<'G'> : sketch_dense_tc_kernel<'U'>;
+    auto kern = mode == 'X' ? sketch_dense_tc_kernel<'X'> : mode == 'G' ? sketch_dense_tc_kernel<'G'> : sketch_dense_tc_kernel<'U'>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) TC_SMEM);
     // Pairs of CTAs that are neighbours along n form a cluster: each generates half of the operator tile and multicasts it
     // (st.async + tcgen05.commit.multicast), which halves the FP64-bound generation per output. Measured on C1: Gaussian
@@ -360,6 +372,79 @@ int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream
         rc = check_launch("tc_reduce_kernel");
     }
     if (a.partial) cudaFreeAsync(a.partial, stream);
+    return rc;
+}
+
+int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
+    if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
+    if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 64 || g.N < 64 || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
+    if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;
+    if (g.alpha == 0.f) return launch_scale_view<float>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
+    if (g.Sx) {      // DenseSkOp::buff given: k-contiguous rows, 16-byte aligned, no ragged float4 at the end of a row
+        if (g.ss_l != 1 || g.ss_i % 4 != 0 || g.K % 4 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0) return RBX_ERR_UNSUPPORTED;
+        return tc_launch(g, 'X', g.Sx, g.ss_i, stream);
+    }
+    // Implicit operator. The fused kernel generates the operator tile from the counter inside the CTA; it needs the parent
+    // rows along k and a 4-aligned column offset. The Gaussian family is bound by the generator (bit-exact Box-Muller,
+    // FP64) because every column tile regenerates the tile at 16 warps per SM, so by default it goes through k-panels
+    // instead when there are more than two column tiles (a CTA pair shares one generated tile): K1 generates each panel
+    // ONCE at full occupancy into a fixed-size float workspace (<= 512 MB however large d * m is; two buffers and an
+    // auxiliary stream when there are several panels) and the same tcgen05 kernel reads it. Measured at C1: fused 1.30 ms,
+    // one panel 0.96 ms (generate 0.18 + contract 0.75 + reduce 0.02); shorter panels lose more to the per-launch ramp and
+    // split-K epilogue than the overlap of generation and contraction returns (4 x 64 MB panels: 1.07 ms).
+    const bool fused_ok = g.l_on_cols && (g.w.pc0 & 3) == 0;
+    bool use_panel = !fused_ok || (g.w.family == 'G' && (g.N + TC_BN - 1) / TC_BN > 2);
+    if (const char* ev = getenv("RBX_TC_PANEL")) { if (atoi(ev) == 0 && fused_ok) use_panel = false; else if (atoi(ev) == 1) use_panel = true; }
+    if (!use_panel) return tc_launch(g, g.w.family, nullptr, 0, stream);
+
+    int64_t kp = ((int64_t) 512 << 20) / (4 * g.M);
+    if (const char* ev = getenv("RBX_TC_PANEL_K")) { const int64_t v = atoll(ev); if (v >= 32) kp = v; }
+    kp = (kp / 32) * 32;
+    if (kp < 256) kp = 256;
+    if (kp > g.K) kp = (g.K + 31) / 32 * 32;
+    const int64_t npanels = (g.K + kp - 1) / kp;
+    const int nbuf = npanels > 1 ? 2 : 1;
+    const size_t panel_elems = (size_t) g.M * (size_t) kp;
+    float* panel = nullptr;
+    if (ws_alloc(&panel, sizeof(float) * panel_elems * nbuf, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    cudaStream_t aux = stream;
+    cudaEvent_t ready = nullptr, filled[2] = { nullptr, nullptr }, used[2] = { nullptr, nullptr };
+    int rc = RBX_OK;
+    if (nbuf == 2) {
+        aux = aux_stream();
+        bool ok = aux != nullptr && cudaEventCreateWithFlags(&ready, cudaEventDisableTiming) == cudaSuccess;
+        for (int b = 0; b < 2 && ok; ++b)
+            ok = cudaEventCreateWithFlags(&filled[b], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&used[b], cudaEventDisableTiming) == cudaSuccess;
+        ok = ok && cudaEventRecord(ready, stream) == cudaSuccess && cudaStreamWaitEvent(aux, ready, 0) == cudaSuccess;
+        if (!ok) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    }
+    GemmOperands<float> gp = g;
+    int64_t p = 0;
+    for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kp, ++p) {
+        const int64_t kl = (l0 + kp <= g.K) ? kp : g.K - l0;
+        const int b = (nbuf == 2) ? (int)(p & 1) : 0;
+        float* buf = panel + (size_t) b * panel_elems;
+        if (nbuf == 2 && p >= 2 && cudaStreamWaitEvent(aux, used[b], 0) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; break; }
+        if (g.l_on_cols) rc = launch_fill_window<float>(g.w.family, g.w.W * 4, buf, g.M, kl, g.w.pr0, g.w.pc0 + l0, g.w.ctr, g.w.key,
+                                                        kp, 1, g.w.family == 'U', aux);
+        else             rc = launch_fill_window<float>(g.w.family, g.w.W * 4, buf, kl, g.M, g.w.pr0 + l0, g.w.pc0, g.w.ctr, g.w.key,
+                                                        1, kp, g.w.family == 'U', aux);
+        if (rc != RBX_OK) break;
+        if (nbuf == 2 && (cudaEventRecord(filled[b], aux) != cudaSuccess || cudaStreamWaitEvent(stream, filled[b], 0) != cudaSuccess)) {
+            cudaGetLastError(); rc = RBX_ERR_CUDA; break;
+        }
+        gp.K = kl; gp.X = g.X + l0; gp.beta = (l0 == 0) ? g.beta : 1.f;
+        rc = tc_launch(gp, 'X', buf, kp, stream);
+        if (rc == RBX_OK && nbuf == 2 && cudaEventRecord(used[b], stream) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    }
+    if (nbuf == 2) {
+        if (rc != RBX_OK) cudaStreamSynchronize(aux);
+        if (ready) cudaEventDestroy(ready);
+        for (int b = 0; b < 2; ++b) { if (filled[b]) cudaEventDestroy(filled[b]); if (used[b]) cudaEventDestroy(used[b]); }
+    }
+    cudaFreeAsync(panel, stream);
     return rc;
 }
 

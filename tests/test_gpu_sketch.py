@@ -122,26 +122,46 @@ def test_sketch_general_dense_medium_ragged(rb, cuda, dt):
         run_dense_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, 1.0, 0.0, off=off, D_extra=(3, 5))
 
 
-def test_sketch_general_dense_tensor_core_path(rb, cuda):
-    """float problems inside the tcgen05 kernel's envelope (rbx_sketch_dense_tc.cu): ragged M / N / K, operator offsets,
-    alpha / beta, both families, and the right-sketch form that maps onto it. The launch count proves the path taken
-    (tensor-core kernel + split-K reduce = 2 launches; the SIMT kernel is 1)."""
-    cases = [("L", "C", "N", "N", 256, 300, 4100, 1.0, 0.0, (0, 0), "G"),
-             ("L", "C", "N", "N", 200, 260, 4096, 1.5, -0.5, (5, 8), "G"),
-             ("L", "C", "N", "N", 128, 512, 2052, 1.0, 0.0, (0, 4), "U"),
-             ("R", "R", "N", "N", 256, 300, 4100, 1.0, 2.0, (0, 0), "G"),
-             ("L", "R", "N", "T", 256, 256, 4096, 1.0, 0.0, (0, 0), "U")]
-    for (side, layout, opS, opA, d, n, m, alpha, beta, off, fam) in cases:
+def test_sketch_general_dense_tensor_core_path(rb, cuda, monkeypatch):
+    """float problems inside the tcgen05 kernel's envelope (rbx_sketch_dense_tc.cu): ragged M / N / K, operator offsets
+    (aligned and not), alpha / beta, both families and major axes, the right-sketch form, a pre-filled operator. The launch
+    count proves the path taken: fused kernel + split-K reduce = 2 launches (uniform family); k-panel form = panels x (panel
+    fill + kernel + reduce) (Gaussian family, or an operator orientation the fused generator does not cover); the SIMT
+    kernel would be 1."""
+    cases = [("L", "C", "N", "N", 256, 300, 4100, 1.0, 0.0, (0, 0), "G", "L", 2),           # two column tiles: fused
+             ("L", "C", "N", "N", 200, 600, 4096, 1.5, -0.5, (5, 8), "G", "L", 3),          # three: k-panel form
+             ("L", "C", "N", "N", 200, 260, 4100, 1.5, -0.5, (5, 7), "G", "L", 3 * 4 + 2),  # unaligned offset; 4 panels of 1024 + one of 4 (no split-K)
+             ("L", "C", "N", "N", 128, 512, 2052, 1.0, 0.0, (0, 4), "U", "L", 2),
+             ("L", "C", "N", "N", 128, 512, 2052, 1.0, 0.5, (2, 1), "U", "S", 3),           # parent rows along i: panel form
+             ("R", "R", "N", "N", 256, 300, 4100, 1.0, 2.0, (0, 0), "G", "L", 2),
+             ("L", "R", "N", "T", 256, 256, 4096, 1.0, 0.0, (0, 0), "U", "L", 2)]
+    for (side, layout, opS, opA, d, n, m, alpha, beta, off, fam, ma, want) in cases:
+        if want > 3:
+            monkeypatch.setenv("RBX_TC_PANEL_K", "1024")
+        else:
+            monkeypatch.delenv("RBX_TC_PANEL_K", raising=False)
         l0 = rb.lib.rbx_launch_count()
         ro, co = off
         if side == "R":
             # B (n x d) = A (n x m) * S (m x d): operator offsets are (rows, cols) of the tall S; its parent is S^T
-            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, m, n, alpha, beta, off=(co, ro), D_extra=(8, 3), fam=fam)
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, m, n, alpha, beta, off=(co, ro), D_extra=(8, 3), fam=fam, ma=ma)
         else:
-            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, n, m, alpha, beta, off=(ro, co), D_extra=(3, 8), fam=fam)
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, n, m, alpha, beta, off=(ro, co), D_extra=(3, 8), fam=fam, ma=ma)
         launches = rb.lib.rbx_launch_count() - l0
-        assert launches == 2, f"expected the tensor-core kernel + reduce, saw {launches} launch(es) for {(side, layout, d, n, m)}"
+        assert launches == want, f"expected {want} launches on the tensor-core path, saw {launches} for {(side, layout, d, n, m, fam, ma)}"
         assert ratio < 0.05      # 3xTF32 with FP32 accumulation sits far inside the FP32 GEMM bound
+    monkeypatch.delenv("RBX_TC_PANEL_K", raising=False)
+    # both forms can be forced (RBX_TC_PANEL) and agree
+    for force, want in (("0", 2), ("1", 3)):
+        monkeypatch.setenv("RBX_TC_PANEL", force)
+        l0 = rb.lib.rbx_launch_count()
+        assert run_dense_case(rb, cuda, "f32", "L", "C", "N", "N", 256, 600, 4100, 1.0, 0.0, D_extra=(3, 8), fam="G") < 0.05
+        assert rb.lib.rbx_launch_count() - l0 == want
+    monkeypatch.delenv("RBX_TC_PANEL", raising=False)
+    # DenseSkOp::buff given (k contiguous): fill_dense(S) + kernel + reduce
+    l0 = rb.lib.rbx_launch_count()
+    assert run_dense_case(rb, cuda, "f32", "L", "C", "N", "N", 192, 256, 4096, 1.0, 0.5, prefilled=True) < 0.05
+    assert rb.lib.rbx_launch_count() - l0 == 3
 
 
 def test_sketch_general_dense_dmma_path(rb, cuda, monkeypatch):
