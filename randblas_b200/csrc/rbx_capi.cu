@@ -144,11 +144,15 @@ static inline void strides_of(char layout, int64_t ld, int64_t* s_row, int64_t* 
 template <typename T>
 static int dispatch_dense_gemm(const GemmOperands<T>& g, cudaStream_t stream);
 template <> int dispatch_dense_gemm<float>(const GemmOperands<float>& g, cudaStream_t stream) {
-    int rc = launch_sketch_dense_tc_f32(g, stream);
+    int rc = launch_sketch_dense_gemv<float>(g, stream);
+    if (rc != RBX_ERR_UNSUPPORTED) return rc;
+    rc = launch_sketch_dense_tc_f32(g, stream);
     return rc == RBX_ERR_UNSUPPORTED ? launch_sketch_dense_simt<float>(g, stream) : rc;
 }
 template <> int dispatch_dense_gemm<double>(const GemmOperands<double>& g, cudaStream_t stream) {
-    int rc = launch_sketch_dense_tc_f64(g, stream);
+    int rc = launch_sketch_dense_gemv<double>(g, stream);
+    if (rc != RBX_ERR_UNSUPPORTED) return rc;
+    rc = launch_sketch_dense_tc_f64(g, stream);
     return rc == RBX_ERR_UNSUPPORTED ? launch_sketch_dense_simt<double>(g, stream) : rc;
 }
 

@@ -431,6 +431,35 @@ def test_sketch_vector(rb, cuda, dt):
 
 
 @pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_sketch_vector_gemv_path(rb, cuda, dt):
+    """sketch_vector at sizes that take the generator-plus-dot-product kernels (rbx_sketch_dense_gemv.cu): both operator
+    orientations (opS, major axis), unaligned offsets, strides, both families; 2 launches (partials + ordered reduce)."""
+    rng = np.random.default_rng(12)
+    npdt = np.float32 if dt == "f32" else np.float64
+    for (d, m, opS, incx, incy, off, fam, ma) in [(300, 5000, "N", 1, 1, (0, 0), "G", "L"), (300, 5000, "N", 2, 3, (3, 5), "U", "L"),
+                                                  (290, 3000, "T", 1, 2, (2, 7), "G", "L"), (300, 2500, "N", 1, 1, (1, 2), "G", "S"),
+                                                  (130, 4099, "T", 3, 1, (0, 1), "U", "S")]:
+        Dr, Dc = d + off[0] + 1, m + off[1] + 2
+        lx, ly = (m, d) if opS == "N" else (d, m)
+        x = rng.standard_normal(lx * incx).astype(npdt)
+        y0 = rng.standard_normal(ly * incy).astype(npdt)
+        S = rb.DenseSkOp(rb.DenseDist(Dr, Dc, fam, ma), 5, dtype=TDT[dt])
+        Sx = dense_S(dt, Dr, Dc, fam, ma, [0, 0, 0, 0], [5, 0], d, m, off[0], off[1])
+        dx, dy = torch.from_numpy(x).to(cuda), torch.from_numpy(y0.copy()).to(cuda)
+        l0 = rb.lib.rbx_launch_count()
+        rb.sketch_vector(rb.Op(opS), d, m, 1.5, S, off[0], off[1], dx, incx, -0.5, dy, incy)
+        assert rb.lib.rbx_launch_count() - l0 == 2
+        Sop = Sx if opS == "N" else Sx.T
+        got_flat = dy.cpu().numpy()
+        got = got_flat[::incy][:ly].astype(np.float64).reshape(-1, 1)
+        check_bound(dt, got, y0[::incy][:ly].astype(np.float64).reshape(-1, 1), Sop, x[::incx][:lx].astype(np.float64).reshape(-1, 1),
+                    1.5, -0.5, "L", ("vector-gemv", opS, fam, ma))
+        if incy > 1:      # the gaps of a strided y are untouched
+            mask = np.ones(len(y0), bool); mask[::incy] = False
+            assert np.array_equal(got_flat[mask], y0[mask])
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_sketch_symmetric(rb, cuda, dt):
     """test_sketch_symmetric.cc:89-155: both sides, both layouts, both major axes; asymmetric input is rejected"""
     rng = np.random.default_rng(4)
