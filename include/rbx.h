@@ -158,6 +158,19 @@ int rbx_spmm_coo_f64(char side, char layout, char opS, char opA, int64_t p0, int
                      int64_t S_rows, int64_t S_cols, int64_t nnz, const int64_t* rows_dev, const int64_t* cols_dev, const double* vals_dev,
                      int64_t ro_s, int64_t co_s, const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
 
+/* ---- sparse format conversion on the device: coo_to_csc / coo_to_csr (conversions.hh:43-62, 84-103, which sort the COO
+ * triplets on the host with sort_coo_data, coo_matrix.hh:267-325) and CSR <-> CSC. by 'C': compressed columns
+ * (ptr_out = colptr, n_cols + 1 entries; idx_out = rowidxs); by 'R': compressed rows (ptr_out = rowptr, n_rows + 1;
+ * idx_out = colidxs). Inner indices come out increasing inside every segment (duplicates ordered by value bits), so the
+ * result is canonical whatever the input order. fmt_in / idx0 / idx1 as for rbx_sketch_sparsedata. Outputs are device
+ * arrays of the caller (nnz entries each, n_outer + 1 for ptr_out). */
+int rbx_sparse_regroup_f32(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const float* vals_dev,
+                           const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t* ptr_out_dev, int64_t* idx_out_dev,
+                           float* vals_out_dev, void* stream);
+int rbx_sparse_regroup_f64(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const double* vals_dev,
+                           const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t* ptr_out_dev, int64_t* idx_out_dev,
+                           double* vals_out_dev, void* stream);
+
 /* ---- sketch_sparse: dense operator x sparse data, sparse_data::lsksp3 / rsksp3, sksp.hh:147-192 / 302-345 */
 /* fmt 'O' COO (idx0 = rows, idx1 = cols), 'R' CSR (idx0 = rowptr, idx1 = colidxs), 'C' CSC (idx0 = rowidxs,
  * idx1 = colptr); int64 indices, index_base Zero. CSR/CSC require ro_a == co_a == 0 (spmm_dispatch.hh:99-104). */

@@ -206,6 +206,51 @@ class CSCMatrix:
     def _idx(self): return self.rowidxs, self.colptr
 
 
+def _regroup(A, by):
+    """device-side conversion to compressed columns ('C') or rows ('R'): rbx_sparse_regroup_* (conversions.hh:43-103)"""
+    n_outer = A.n_cols if by == "C" else A.n_rows
+    i0, i1 = A._idx()
+    ptr = torch.empty(n_outer + 1, dtype=torch.int64, device=A.vals.device)
+    idx = torch.empty(A.nnz, dtype=torch.int64, device=A.vals.device)
+    vals = torch.empty_like(A.vals)
+    _call(f"rbx_sparse_regroup_{_suf(A.vals.dtype)}", _c(by), _c(A.fmt), A.n_rows, A.n_cols, A.nnz, _ptr(A.vals), _ptr(i0), _ptr(i1),
+          _ptr(ptr), _ptr(idx), _ptr(vals), _stream(A.vals))
+    return ptr, idx, vals
+
+
+def coo_to_csc(coo):
+    """conversions::coo_to_csc (conversions.hh:43-62): the sort and the compression run on the device"""
+    ptr, idx, vals = _regroup(coo, "C")
+    return CSCMatrix(coo.n_rows, coo.n_cols, vals, idx, ptr)
+
+
+def coo_to_csr(coo):
+    """conversions::coo_to_csr (conversions.hh:84-103)"""
+    ptr, idx, vals = _regroup(coo, "R")
+    return CSRMatrix(coo.n_rows, coo.n_cols, vals, ptr, idx)
+
+
+def csr_to_csc(csr):
+    """CSR -> CSC of the same matrix (a data-moving transpose; transpose_as_csc, conversions.hh:143-159, is the zero-copy view)"""
+    ptr, idx, vals = _regroup(csr, "C")
+    return CSCMatrix(csr.n_rows, csr.n_cols, vals, idx, ptr)
+
+
+def csc_to_csr(csc):
+    ptr, idx, vals = _regroup(csc, "R")
+    return CSRMatrix(csc.n_rows, csc.n_cols, vals, ptr, idx)
+
+
+def transpose_as_csr(csc):
+    """conversions::transpose_as_csr (conversions.hh:125-141): the CSC arrays of A are the CSR arrays of A^T (shared memory)"""
+    return CSRMatrix(csc.n_cols, csc.n_rows, csc.vals, csc.colptr, csc.rowidxs)
+
+
+def transpose_as_csc(csr):
+    """conversions::transpose_as_csc (conversions.hh:143-159)"""
+    return CSCMatrix(csr.n_cols, csr.n_rows, csr.vals, csr.colidxs, csr.rowptr)
+
+
 # ---- fills ---------------------------------------------------------------------------------------------
 def fill_dense_submat(family, n_cols, smat, n_srows, n_scols, ptr, seed, lda=0):
     """dense::fill_dense_submat_impl (dense_skops.hh:96-170); returns the next state."""

@@ -452,6 +452,37 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
     return rc;
 }
 
+// ---- sparse format conversion -----------------------------------------------------------------------
+template <typename T>
+static int sparse_regroup(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const T* vals, const int64_t* idx0,
+                          const int64_t* idx1, int64_t* ptr_out, int64_t* idx_out, T* vals_out, void* stream) {
+    RBX_REQUIRE(by == 'C' || by == 'R');
+    RBX_REQUIRE(fmt_in == 'O' || fmt_in == 'R' || fmt_in == 'C');
+    RBX_REQUIRE(n_rows >= 0 && n_cols >= 0 && nnz >= 0);
+    RBX_NEED_DEVICE();
+    cudaStream_t st = (cudaStream_t) stream;
+    const int64_t n_outer = (by == 'C') ? n_cols : n_rows, n_inner = (by == 'C') ? n_rows : n_cols;
+    const int64_t *prow = idx0, *pcol = idx1;
+    int64_t* expanded = nullptr;
+    int rc = RBX_OK;
+    if (fmt_in != 'O' && nnz > 0) {
+        if (ws_alloc(&expanded, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+        rc = (fmt_in == 'R') ? launch_expand_ptr(n_rows, idx0, expanded, st) : launch_expand_ptr(n_cols, idx1, expanded, st);
+        if (fmt_in == 'R') { prow = expanded; pcol = idx1; } else { prow = idx0; pcol = expanded; }
+    }
+    int64_t *ptr = nullptr, *lidx = nullptr; T* v = nullptr;
+    // grouping by columns keeps (l, j) = (row, col); grouping by rows swaps the roles
+    if (rc == RBX_OK) rc = spd_group_by_column<T>(nnz, prow, pcol, vals, by == 'R', 0, 0, n_inner, n_outer, &ptr, &lidx, &v, st);
+    if (expanded) cudaFreeAsync(expanded, st);
+    if (rc != RBX_OK) return rc;
+    bool ok = cudaMemcpyAsync(ptr_out, ptr, 8 * (size_t)(n_outer + 1), cudaMemcpyDeviceToDevice, st) == cudaSuccess;
+    if (nnz > 0) ok = ok && cudaMemcpyAsync(idx_out, lidx, 8 * (size_t) nnz, cudaMemcpyDeviceToDevice, st) == cudaSuccess &&
+                      cudaMemcpyAsync(vals_out, v, sizeof(T) * (size_t) nnz, cudaMemcpyDeviceToDevice, st) == cudaSuccess;
+    cudaFreeAsync(ptr, st); cudaFreeAsync(lidx, st); cudaFreeAsync(v, st);
+    if (!ok) { cudaGetLastError(); return RBX_ERR_CUDA; }
+    return RBX_OK;
+}
+
 }  // namespace rbx
 
 // =====================================================================================================
@@ -605,6 +636,17 @@ RBX_DEF_SPARSE(f32_i32, float, int32_t)
 RBX_DEF_SPARSE(f32_i64, float, int64_t)
 RBX_DEF_SPARSE(f64_i32, double, int32_t)
 RBX_DEF_SPARSE(f64_i64, double, int64_t)
+
+int rbx_sparse_regroup_f32(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const float* vals_dev,
+                           const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t* ptr_out_dev, int64_t* idx_out_dev,
+                           float* vals_out_dev, void* stream) {
+    return sparse_regroup<float>(by, fmt_in, n_rows, n_cols, nnz, vals_dev, idx0_dev, idx1_dev, ptr_out_dev, idx_out_dev, vals_out_dev, stream);
+}
+int rbx_sparse_regroup_f64(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const double* vals_dev,
+                           const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t* ptr_out_dev, int64_t* idx_out_dev,
+                           double* vals_out_dev, void* stream) {
+    return sparse_regroup<double>(by, fmt_in, n_rows, n_cols, nnz, vals_dev, idx0_dev, idx1_dev, ptr_out_dev, idx_out_dev, vals_out_dev, stream);
+}
 
 int rbx_malloc(void** dev_ptr, uint64_t bytes) {
     if (!dev_ptr) return RBX_ERR_ARG;

@@ -272,6 +272,7 @@ int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, c
         spd_scatter_kernel<T><<<(unsigned) blocks, 256, 0, stream>>>(nnz, prow, pcol, vals, trans, ro, co, K, N, cursor, tmp);
         int64_t sb = (N * 32 + 255) / 256;
         if (sb > kNumSMs * 32) sb = kNumSMs * 32;
+        if (sb < 1) sb = 1;
         spd_segment_sort_kernel<T><<<(unsigned) sb, 256, 0, stream>>>(N, ptr, tmp, out_l, out_v, K < 0x7fffffffll);
         for (int q = 0; q < 6; ++q) count_launch();
         rc = check_launch("spd_group_by_column");

@@ -403,6 +403,31 @@ def test_sketch_sparse_medium_slabs_and_determinism(rb, cuda, fmt, monkeypatch):
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
 
 
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_sparse_conversions_on_device(rb, cuda, dt):
+    """conversions.hh:43-159 on the device (rbx_sparse_regroup_*): COO -> CSC / CSR from shuffled triplets, CSR <-> CSC,
+    the zero-copy transpose views, empty rows / columns, an empty matrix; results equal scipy's canonical forms exactly."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(21)
+    npdt = np.float32 if dt == "f32" else np.float64
+    for (r, c, dens) in [(40, 70, 0.1), (300, 50, 0.3), (64, 64, 0.0), (5, 2000, 0.02)]:
+        M = random_sparse(rng, r, c, dens, npdt)
+        coo = sp.coo_matrix(M)
+        perm = rng.permutation(coo.nnz)
+        t = lambda a, d=None: torch.from_numpy(np.ascontiguousarray(a if d is None else a.astype(d))).to(cuda)
+        A = rb.COOMatrix(r, c, t(coo.data[perm]), t(coo.row[perm], np.int64), t(coo.col[perm], np.int64))
+        want_csc, want_csr = sp.csc_matrix(M), sp.csr_matrix(M)
+        want_csc.sort_indices(); want_csr.sort_indices()
+        for got, want, ptr, idx in [(rb.coo_to_csc(A), want_csc, "colptr", "rowidxs"), (rb.coo_to_csr(A), want_csr, "rowptr", "colidxs"),
+                                    (rb.csr_to_csc(to_fmt(rb, cuda, M, "R")), want_csc, "colptr", "rowidxs"),
+                                    (rb.csc_to_csr(to_fmt(rb, cuda, M, "C")), want_csr, "rowptr", "colidxs")]:
+            assert np.array_equal(getattr(got, ptr).cpu().numpy(), want.indptr)
+            assert np.array_equal(getattr(got, idx).cpu().numpy(), want.indices)
+            assert np.array_equal(got.vals.cpu().numpy(), want.data)
+        At = rb.transpose_as_csr(rb.coo_to_csc(A))
+        assert (At.n_rows, At.n_cols) == (c, r) and np.array_equal(At.rowptr.cpu().numpy(), want_csc.indptr)
+
+
 # ---------------------------------------------------------------------------------------------- wrappers
 @pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_sketch_vector(rb, cuda, dt):
