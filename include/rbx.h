@@ -158,6 +158,21 @@ int rbx_spmm_coo_f64(char side, char layout, char opS, char opA, int64_t p0, int
                      int64_t S_rows, int64_t S_cols, int64_t nnz, const int64_t* rows_dev, const int64_t* cols_dev, const double* vals_dev,
                      int64_t ro_s, int64_t co_s, const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
 
+/* ---- index sampling utilities, util.hh:257-334 (same Philox + uneg11 stream as the reference, bit for bit) ----
+ * rbx_sample_indices_iid_uniform: util::sample_indices_iid_uniform (util.hh:311-334), k samples of {0..n-1};
+ * rbx_sample_indices_iid_*:       util::sample_indices_iid (util.hh:284-305), lower_bound in a device-resident cdf;
+ * rbx_weights_to_cdf_*:           util::weights_to_cdf (util.hh:257-270), in place; RBX_ERR_ARG where the reference throws
+ *                                 (a weight below error_if_below, or a total below sqrt(n) * eps); synchronises the stream.
+ * next_ctr (may be NULL) receives the returned state's counter: ctr + ceil(k / 4) for k > 0. */
+int rbx_sample_indices_iid_uniform(int64_t n, int64_t k, int64_t* samples_dev, const uint32_t ctr[4], const uint32_t key[2],
+                                   uint32_t next_ctr[4], void* stream);
+int rbx_sample_indices_iid_f32(int64_t n, const float* cdf_dev, int64_t k, int64_t* samples_dev, const uint32_t ctr[4],
+                               const uint32_t key[2], uint32_t next_ctr[4], void* stream);
+int rbx_sample_indices_iid_f64(int64_t n, const double* cdf_dev, int64_t k, int64_t* samples_dev, const uint32_t ctr[4],
+                               const uint32_t key[2], uint32_t next_ctr[4], void* stream);
+int rbx_weights_to_cdf_f32(int64_t n, float* w_dev, float error_if_below, void* stream);
+int rbx_weights_to_cdf_f64(int64_t n, double* w_dev, double error_if_below, void* stream);
+
 /* ---- sparse format conversion on the device: coo_to_csc / coo_to_csr (conversions.hh:43-62, 84-103, which sort the COO
  * triplets on the host with sort_coo_data, coo_matrix.hh:267-325) and CSR <-> CSC. by 'C': compressed columns
  * (ptr_out = colptr, n_cols + 1 entries; idx_out = rowidxs); by 'R': compressed rows (ptr_out = rowptr, n_rows + 1;

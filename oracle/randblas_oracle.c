@@ -556,3 +556,63 @@ int orc_sketch_sparsedata_##SUF(char side, char layout, char opS, char opA, int6
 }
 DEF_SK_SPARSEDATA(f32, float, 1)
 DEF_SK_SPARSEDATA(f64, double, 0)
+
+/* ------------------------------------------------------------------------------------------
+ * Index sampling utilities (util.hh:257-334).
+ * sample_indices_iid_uniform (:311-334) / sample_indices_iid (:284-305): the loop increments the counter BEFORE the first
+ * draw ((i + 1) % 4 == 1 at i = 0), so sample i uses lane i % 4 of uneg11(philox(ctr + 1 + i / 4)); the value is mapped to
+ * [0, 1] as (x + 1) / 2 in TF precision (double for the uniform form), then index = trunc(n * u) (uniform: `(int64_t) dN *
+ * u` parses as ((int64_t) dN) * u, a double product truncated on assignment) or lower_bound(cdf, u).
+ * Returned state: ctr + ceil(k / 4) for k > 0, ctr for k = 0.
+ * weights_to_cdf (:257-270): sequential running sum in T (order matters), negatives >= error_if_below clipped to 0,
+ * then scaled by 1 / sum with blas::scal; rc 1 where the reference throws.
+ * ---------------------------------------------------------------------------------------- */
+static float orc_sample_lane(const uint32_t ctr[4], const uint32_t key[2], int64_t i) {
+    uint32_t c[4] = { ctr[0], ctr[1], ctr[2], ctr[3] }, rv[4];
+    orc_ctr_add(c, (uint64_t)(1 + i / 4));
+    orc_philox4x32_10(c, key, rv);
+    return orc_uneg11(rv[i % 4]);
+}
+static void orc_sample_next(const uint32_t ctr[4], int64_t k, uint32_t next_ctr[4]) {
+    if (!next_ctr) return;
+    for (int q = 0; q < 4; ++q) next_ctr[q] = ctr[q];
+    if (k > 0) orc_ctr_add(next_ctr, (uint64_t)((k + 3) / 4));
+}
+int orc_sample_indices_iid_uniform(int64_t n, int64_t k, int64_t* samples, const uint32_t ctr[4], const uint32_t key[2],
+                                   uint32_t next_ctr[4]) {
+    const double dN = (double) n;
+    for (int64_t i = 0; i < k; ++i) {
+        const double u = ((double) orc_sample_lane(ctr, key, i) + 1.0) / 2.0;
+        samples[i] = (int64_t)((double)(int64_t) dN * u);
+    }
+    orc_sample_next(ctr, k, next_ctr);
+    return 0;
+}
+#define DEF_SAMPLE(SUF, T)                                                                              \
+int orc_sample_indices_iid_##SUF(int64_t n, const T* cdf, int64_t k, int64_t* samples, const uint32_t ctr[4], \
+                                 const uint32_t key[2], uint32_t next_ctr[4]) {                           \
+    for (int64_t i = 0; i < k; ++i) {                                                                     \
+        const T u = ((T) orc_sample_lane(ctr, key, i) + (T) 1.0) / (T) 2.0;                               \
+        int64_t lo = 0, hi = n;               /* std::lower_bound: first index with cdf[idx] >= u */     \
+        while (lo < hi) { const int64_t mid = lo + (hi - lo) / 2; if (cdf[mid] < u) lo = mid + 1; else hi = mid; } \
+        samples[i] = lo;                                                                                  \
+    }                                                                                                     \
+    orc_sample_next(ctr, k, next_ctr);                                                                    \
+    return 0;                                                                                             \
+}                                                                                                         \
+int orc_weights_to_cdf_##SUF(int64_t n, T* w, T error_if_below) {                                         \
+    T sum = (T) 0.0;                                                                                      \
+    for (int64_t i = 0; i < n; ++i) {                                                                     \
+        T val = w[i];                                                                                     \
+        if (!(val >= error_if_below)) return 1;                                                           \
+        val = val > (T) 0.0 ? val : (T) 0.0;                                                              \
+        sum += val;                                                                                       \
+        w[i] = sum;                                                                                       \
+    }                                                                                                     \
+    if (!(sum >= ((T) sqrt((double) n)) * (sizeof(T) == 4 ? (T) 0x1p-23 : (T) 0x1p-52))) return 1;        \
+    const T inv = ((T) 1.0) / sum;                                                                        \
+    for (int64_t i = 0; i < n; ++i) w[i] = inv * w[i];                                                    \
+    return 0;                                                                                             \
+}
+DEF_SAMPLE(f32, float)
+DEF_SAMPLE(f64, double)

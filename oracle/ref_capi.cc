@@ -258,3 +258,31 @@ DEF_SK_SYMM(f32, float)
 DEF_SK_SYMM(f64, double)
 
 }  // extern "C"
+
+// ---- index sampling utilities (util.hh:257-334) ----------------------------------------
+extern "C" {
+
+int ref_sample_indices_iid_uniform(int64_t n, int64_t k, int64_t* samples, const uint32_t* ctr, const uint32_t* key,
+                                   uint32_t* next_ctr) {
+    REF_TRY
+    State out = RandBLAS::util::sample_indices_iid_uniform(n, k, samples, mk_state(ctr, key));
+    put_ctr(out, next_ctr);
+    REF_CATCH
+}
+#define DEF_SAMPLE(SUF, T)                                                                                  \
+int ref_sample_indices_iid_##SUF(int64_t n, T* cdf, int64_t k, int64_t* samples, const uint32_t* ctr,        \
+                                 const uint32_t* key, uint32_t* next_ctr) {                                  \
+    REF_TRY                                                                                                 \
+    State out = RandBLAS::util::sample_indices_iid(n, cdf, k, samples, mk_state(ctr, key));                  \
+    put_ctr(out, next_ctr);                                                                                 \
+    REF_CATCH                                                                                               \
+}                                                                                                           \
+int ref_weights_to_cdf_##SUF(int64_t n, T* w, T error_if_below) {                                           \
+    REF_TRY                                                                                                 \
+    RandBLAS::util::weights_to_cdf(n, w, error_if_below);                                                   \
+    REF_CATCH                                                                                               \
+}
+DEF_SAMPLE(f32, float)
+DEF_SAMPLE(f64, double)
+
+}  // extern "C"

@@ -297,6 +297,29 @@ def repeated_fisher_yates(state, vec_nnz, dim_major, dim_minor, idxs_major, idxs
     return state.copy()
 
 
+def sample_indices_iid_uniform(n, k, samples, state):
+    """util::sample_indices_iid_uniform (util.hh:311-334): k iid samples of {0..n-1} into the int64 device tensor
+    `samples`; returns the next state."""
+    nx = _u32([0] * 4)
+    _call("rbx_sample_indices_iid_uniform", n, k, _ptr(samples), _u32(state.counter), _u32(state.key), nx, _stream(samples))
+    return RNGState(state.key, list(nx))
+
+
+def sample_indices_iid(n, cdf, k, samples, state):
+    """util::sample_indices_iid (util.hh:284-305): k iid samples from the distribution whose cdf is the device tensor `cdf`."""
+    nx = _u32([0] * 4)
+    _call(f"rbx_sample_indices_iid_{_suf(cdf.dtype)}", n, _ptr(cdf), k, _ptr(samples), _u32(state.counter), _u32(state.key), nx,
+          _stream(samples))
+    return RNGState(state.key, list(nx))
+
+
+def weights_to_cdf(n, w, error_if_below=None):
+    """util::weights_to_cdf (util.hh:257-270), in place on the device tensor w; raises Error where the reference throws."""
+    if error_if_below is None:
+        error_if_below = -float(torch.finfo(w.dtype).eps)
+    _call(f"rbx_weights_to_cdf_{_suf(w.dtype)}", n, _ptr(w), error_if_below, _stream(w))
+
+
 def fill_sparse(S, device=None):
     """fill_sparse(SparseSkOp&) (sparse_skops.hh:389-413)."""
     dev = device or torch.device("cuda", torch.cuda.current_device())

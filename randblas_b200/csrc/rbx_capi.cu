@@ -648,6 +648,41 @@ int rbx_sparse_regroup_f64(char by, char fmt_in, int64_t n_rows, int64_t n_cols,
     return sparse_regroup<double>(by, fmt_in, n_rows, n_cols, nnz, vals_dev, idx0_dev, idx1_dev, ptr_out_dev, idx_out_dev, vals_out_dev, stream);
 }
 
+static void sample_next_ctr(const uint32_t ctr[4], int64_t k, uint32_t next_ctr[4]) {
+    if (next_ctr) put_ctr(k > 0 ? ctr_add(mk_ctr(ctr), (uint64_t)((k + 3) / 4)) : mk_ctr(ctr), next_ctr);
+}
+int rbx_sample_indices_iid_uniform(int64_t n, int64_t k, int64_t* samples_dev, const uint32_t ctr[4], const uint32_t key[2],
+                                   uint32_t next_ctr[4], void* stream) {
+    RBX_REQUIRE(n >= 0 && k >= 0);
+    sample_next_ctr(ctr, k, next_ctr);
+    RBX_NEED_DEVICE();
+    return launch_sample_uniform(n, k, samples_dev, mk_ctr(ctr), mk_key(key), (cudaStream_t) stream);
+}
+int rbx_sample_indices_iid_f32(int64_t n, const float* cdf_dev, int64_t k, int64_t* samples_dev, const uint32_t ctr[4],
+                               const uint32_t key[2], uint32_t next_ctr[4], void* stream) {
+    RBX_REQUIRE(n >= 0 && k >= 0);
+    sample_next_ctr(ctr, k, next_ctr);
+    RBX_NEED_DEVICE();
+    return launch_sample_cdf<float>(n, cdf_dev, k, samples_dev, mk_ctr(ctr), mk_key(key), (cudaStream_t) stream);
+}
+int rbx_sample_indices_iid_f64(int64_t n, const double* cdf_dev, int64_t k, int64_t* samples_dev, const uint32_t ctr[4],
+                               const uint32_t key[2], uint32_t next_ctr[4], void* stream) {
+    RBX_REQUIRE(n >= 0 && k >= 0);
+    sample_next_ctr(ctr, k, next_ctr);
+    RBX_NEED_DEVICE();
+    return launch_sample_cdf<double>(n, cdf_dev, k, samples_dev, mk_ctr(ctr), mk_key(key), (cudaStream_t) stream);
+}
+int rbx_weights_to_cdf_f32(int64_t n, float* w_dev, float error_if_below, void* stream) {
+    RBX_REQUIRE(n >= 0);
+    RBX_NEED_DEVICE();
+    return launch_weights_to_cdf<float>(n, w_dev, error_if_below, (cudaStream_t) stream);
+}
+int rbx_weights_to_cdf_f64(int64_t n, double* w_dev, double error_if_below, void* stream) {
+    RBX_REQUIRE(n >= 0);
+    RBX_NEED_DEVICE();
+    return launch_weights_to_cdf<double>(n, w_dev, error_if_below, (cudaStream_t) stream);
+}
+
 int rbx_malloc(void** dev_ptr, uint64_t bytes) {
     if (!dev_ptr) return RBX_ERR_ARG;
     *dev_ptr = nullptr;

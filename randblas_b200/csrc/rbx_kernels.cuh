@@ -19,6 +19,12 @@ template <typename T, typename I>
 int launch_fisher_yates(const Ctr128& ctr, const Key64& key, int64_t vec_nnz, int64_t dim_major, int64_t dim_minor,
                         I* idxs_major, I* idxs_minor, T* vals, cudaStream_t stream);
 
+// ---- index sampling utilities (rbx_sample.cu; util.hh:257-334) ------------------------------------------
+int launch_sample_uniform(int64_t n, int64_t k, int64_t* samples, const Ctr128& ctr, const Key64& key, cudaStream_t stream);
+template <typename T>
+int launch_sample_cdf(int64_t n, const T* cdf, int64_t k, int64_t* samples, const Ctr128& ctr, const Key64& key, cudaStream_t stream);
+template <typename T> int launch_weights_to_cdf(int64_t n, T* w, T error_if_below, cudaStream_t stream);
+
 // ---- K2 -------------------------------------------------------------------------------------------
 // C[i, j] = alpha * sum_l Sop[i, l] * X[l, j] + beta * C[i, j]
 template <typename T>

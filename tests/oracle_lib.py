@@ -165,3 +165,29 @@ def dense_next_state(n_rows, n_cols, major_axis, ctr):
     out = u32([0] * 4)
     ORC.orc_dense_next_state(c_i64(n_rows), c_i64(n_cols), ch(major_axis), u32(ctr), out)
     return list(out)
+
+
+# ---- index sampling utilities (util.hh:257-334) -----------------------------------------------------
+def sample_indices_iid_uniform(n, k, ctr, key, which="orc"):
+    lib, pre = _lib(which)
+    out = np.zeros(max(k, 1), np.int64)
+    nx = u32([0] * 4)
+    rc = getattr(lib, pre + "sample_indices_iid_uniform")(ctypes.c_int64(n), ctypes.c_int64(k), ptr(out), u32(ctr), u32(key), nx)
+    return rc, out[:k], list(nx)
+
+
+def sample_indices_iid(dt, cdf, k, ctr, key, which="orc"):
+    lib, pre = _lib(which)
+    cdf = np.ascontiguousarray(cdf, _np(dt))
+    out = np.zeros(max(k, 1), np.int64)
+    nx = u32([0] * 4)
+    rc = getattr(lib, f"{pre}sample_indices_iid_{dt}")(ctypes.c_int64(len(cdf)), ptr(cdf), ctypes.c_int64(k), ptr(out), u32(ctr), u32(key), nx)
+    return rc, out[:k], list(nx)
+
+
+def weights_to_cdf(dt, w, error_if_below=None, which="orc"):
+    lib, pre = _lib(which)
+    w = np.array(w, _np(dt))
+    eib = -np.finfo(_np(dt)).eps if error_if_below is None else error_if_below
+    rc = getattr(lib, f"{pre}weights_to_cdf_{dt}")(ctypes.c_int64(len(w)), ptr(w), _sc(dt, eib))
+    return rc, w

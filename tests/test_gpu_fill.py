@@ -210,3 +210,35 @@ def test_repeated_fisher_yates_workarray_path(rb, cuda):
     assert rc == 0 and np.array_equal(idx.cpu().numpy(), rows)
     for v in idx.view(r, k).cpu().numpy():
         assert len(set(v.tolist())) == k
+
+
+# ---- index sampling utilities (util.hh:257-334): bit-exact against the oracle ------------------------------------
+@pytest.mark.parametrize("n,k", [(10, 0), (10, 1), (7, 4), (1000, 5), (1 << 20, 100003), (3, 64)])
+def test_sample_indices_iid_uniform(rb, cuda, n, k):
+    ctr, key = [0xFFFFFFFE, 0xFFFFFFFF, 0, 0], [42, 0]
+    out = torch.full((max(k, 1),), -7, dtype=torch.int64, device=cuda)
+    nxt = rb.sample_indices_iid_uniform(n, k, out, rb.RNGState(key, ctr))
+    rc, want, nx = ol.sample_indices_iid_uniform(n, k, ctr, key)
+    assert rc == 0 and np.array_equal(out.cpu().numpy()[:k], want) and list(nxt.counter) == nx
+    if k == 0:
+        assert int(out[0]) == -7
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_weights_to_cdf_and_sample_indices_iid(rb, cuda, dt):
+    tdt = torch.float32 if dt == "f32" else torch.float64
+    rng = np.random.default_rng(3)
+    for n, k in [(1, 5), (17, 40), (1000, 1003), (100000, 20001)]:
+        w = rng.random(n)
+        w[rng.random(n) < 0.2] = 0.0
+        dw = torch.from_numpy(w).to(tdt).to(cuda)
+        rb.weights_to_cdf(n, dw)
+        rc, cdf = ol.weights_to_cdf(dt, w)
+        assert rc == 0 and np.array_equal(dw.cpu().numpy().view(np.uint8), cdf.view(np.uint8))      # sequential sum: same bits
+        out = torch.zeros(k, dtype=torch.int64, device=cuda)
+        nxt = rb.sample_indices_iid(n, dw, k, out, rb.RNGState([7, 1], [5, 0, 0, 0]))
+        rc, want, nx = ol.sample_indices_iid(dt, cdf, k, [5, 0, 0, 0], [7, 1])
+        assert rc == 0 and np.array_equal(out.cpu().numpy(), want) and list(nxt.counter) == nx
+    for bad in ([0.5, -0.1, 0.5], [0.0, 0.0, 0.0]):
+        with pytest.raises(rb.Error):
+            rb.weights_to_cdf(3, torch.tensor(bad, dtype=tdt, device=cuda))

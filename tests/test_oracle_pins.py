@@ -142,3 +142,32 @@ def test_oracle_sketch_definitions_vs_reference():
                     assert ol.sketch_dense(*args, Ba, ldb, "orc") == 0
                     assert ol.sketch_dense(*args, Bb, ldb, "ref") == 0
                     assert np.allclose(Ba, Bb, rtol=0, atol=1.5 * m * 2 * eps * 40 + 0.5 * eps * 4), (dt, side, lay, opS)
+
+
+# ---- index sampling utilities: restatement vs the compiled reference (util.hh:257-334) --------------------------
+@pytest.mark.skipif(ol.REF is None, reason="compiled reference not built")
+@pytest.mark.parametrize("n,k", [(10, 0), (10, 1), (7, 4), (1000, 5), (1 << 20, 1001), (3, 64)])
+def test_sample_indices_iid_uniform_matches_reference(n, k):
+    ctr, key = [0xFFFFFFFE, 0xFFFFFFFF, 0, 0], [42, 0]          # counter carries into the third word
+    rc_o, s_o, nx_o = ol.sample_indices_iid_uniform(n, k, ctr, key, "orc")
+    rc_r, s_r, nx_r = ol.sample_indices_iid_uniform(n, k, ctr, key, "ref")
+    assert rc_o == rc_r == 0 and np.array_equal(s_o, s_r) and nx_o == nx_r
+    assert (s_o >= 0).all() and (s_o <= n).all()
+
+
+@pytest.mark.skipif(ol.REF is None, reason="compiled reference not built")
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_weights_to_cdf_and_sample_indices_iid_match_reference(dt):
+    rng = np.random.default_rng(3)
+    for n, k in [(1, 5), (17, 40), (1000, 1003)]:
+        w = rng.random(n)
+        w[rng.random(n) < 0.2] = 0.0                                # flat stretches in the cdf
+        rc_o, cdf_o = ol.weights_to_cdf(dt, w, which="orc")
+        rc_r, cdf_r = ol.weights_to_cdf(dt, w, which="ref")
+        assert rc_o == rc_r == 0 and np.array_equal(cdf_o.view(np.uint8), cdf_r.view(np.uint8))
+        rc_o, s_o, nx_o = ol.sample_indices_iid(dt, cdf_o, k, [5, 0, 0, 0], [7, 1], "orc")
+        rc_r, s_r, nx_r = ol.sample_indices_iid(dt, cdf_o, k, [5, 0, 0, 0], [7, 1], "ref")
+        assert rc_o == rc_r == 0 and np.array_equal(s_o, s_r) and nx_o == nx_r
+    # the reference throws on a weight below the threshold and on an all-zero vector
+    for bad in ([0.5, -0.1, 0.5], [0.0, 0.0, 0.0]):
+        assert ol.weights_to_cdf(dt, bad, which="orc")[0] != 0 and ol.weights_to_cdf(dt, bad, which="ref")[0] != 0
