@@ -53,6 +53,8 @@ __global__ void __launch_bounds__(256) fill_dense_kernel(T* __restrict__ out, co
     int64_t i, b;
     if (p.rows_fastest) { b = tid / p.n_srows; i = tid - b * p.n_srows; }
     else                { i = tid / p.nblk;    b = tid - i * p.nblk; }
+    double kr[14];
+    if (FAMILY == 'G') hoist_bm_consts(kr);
     // running counter offset and output pointer, advanced by the (rows, blocks) stride with one wrap correction
     uint64_t coff = (uint64_t)((p.r0 + i) * p.W + p.blk0 + b);
     T* dst = out + i * p.rs + ((p.blk0 + b) * 4 - p.c0) * p.cs;
@@ -62,7 +64,7 @@ __global__ void __launch_bounds__(256) fill_dense_kernel(T* __restrict__ out, co
     const int64_t dst_wrap = p.rows_fastest ? 4 * p.cs - p.n_srows * p.rs : p.rs - p.nblk * 4 * p.cs;
     for (int64_t it = tid; it < p.items; it += (int64_t) gridDim.x * blockDim.x) {
         const Ctr128 c = ctr_add(p.ctr, coff);
-        const float4 v = generate4<FAMILY>(philox4x32_10(c, p.key), tab);
+        const float4 v = generate4<FAMILY>(philox4x32_10(c, p.key), tab, kr);
         const T e0 = cast_scale<T>(v.x, scale, do_scale), e1 = cast_scale<T>(v.y, scale, do_scale),
                 e2 = cast_scale<T>(v.z, scale, do_scale), e3 = cast_scale<T>(v.w, scale, do_scale);
         if (VEC) {
