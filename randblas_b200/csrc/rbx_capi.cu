@@ -357,6 +357,15 @@ static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p
                                            A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
         if (rc != RBX_ERR_UNSUPPORTED) return rc;
     }
+    // A tall Short-axis operator used transposed (the usual right sketch B = A * S, S n x d) is the wide operator of the
+    // transposed shape with the same state: fill_sparse draws one Fisher-Yates vector over the short axis per long-axis
+    // index either way (sparse_skops.hh:392-410), only the roles of rows and columns swap. Square operators count as wide
+    // there (:394), so their transpose is not of this form.
+    if (s.s_trans && major_axis == 'S' && S_rows > S_cols) {
+        const int rc = launch_saso_fast<T>(mk_ctr(ctr), mk_key(key), S_cols, S_rows, vec_nnz, co_s, ro_s, s.M, s.N, s.K, alpha,
+                                           A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
+        if (rc != RBX_ERR_UNSUPPORTED) return rc;
+    }
     RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));
     if (alpha == (T) 0) return RBX_OK;
     const size_t nnz = (size_t)(vec_nnz * (major_axis == 'S' ? lng : sht));

@@ -284,6 +284,11 @@ def test_saso_medium(rb, cuda, dt):
         run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 256, 96, 16384, 1.0, 0.0, 8, "S", key=1997)
         run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 200, 100, 10001, 2.0, 1.0, 8, "S", key=1997, off=(5, 1234), D_extra=(51, 77))
         run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 2048, 64, 4096, 1.0, 0.0, 8, "S", key=7)
+        # the usual right sketch B = A * S with a tall SASO S (and its left form with opS = Trans): same streaming kernel,
+        # the operator being the wide one of the transposed shape with the same state
+        run_sparseop_case(rb, cuda, dt, "R", layout, "N", "N", 256, 96, 16384, 1.0, 0.0, 8, "S", key=1997)
+        run_sparseop_case(rb, cuda, dt, "R", layout, "N", "T", 200, 100, 10001, 2.0, 1.0, 8, "S", key=1997, off=(1234, 5), D_extra=(77, 51))
+        run_sparseop_case(rb, cuda, dt, "L", layout, "T", "N", 256, 96, 16384, 1.5, 0.0, 8, "S", key=3)
 
 
 @pytest.mark.parametrize("dt", ["f32", "f64"])
