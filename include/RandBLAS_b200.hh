@@ -23,6 +23,7 @@
 #include <stdexcept>
 #include <string>
 #include <type_traits>
+#include <limits>
 #include <vector>
 #include <algorithm>
 #include <cmath>
@@ -526,6 +527,47 @@ inline void require_symmetric(blas::Layout layout, const T* A, int64_t n, int64_
             const T viol = std::abs(Aij - Aji), rel_tol = (std::abs(Aij) + std::abs(Aji) + 1) * tol;
             if (viol > rel_tol) throw Error("Symmetry check failed, in function require_symmetric");
         }
+}
+// ---- index sampling (util.hh:257-334): same Philox + uneg11 stream and returned state as the reference ----------
+// run body(dev_ptr) on a device copy of a host array of `bytes` bytes (in/out), or on the pointer itself in device mode
+template <typename F>
+inline void with_device_(void* host_or_dev, uint64_t bytes, bool copy_in, bool copy_out, F body) {
+    if (device_pointers() || bytes == 0) { body(host_or_dev); return; }
+    detail::DevBuf d;
+    if (copy_in) d.upload(host_or_dev, bytes); else d.alloc(bytes);
+    body(d.p);
+    if (copy_out) detail::check(rbx_memcpy_d2h(host_or_dev, d.p, bytes, nullptr), "rbx_memcpy_d2h");
+}
+
+template <typename T>
+inline void weights_to_cdf(int64_t n, T* w, T error_if_below = -std::numeric_limits<T>::epsilon()) {      // util.hh:257-270
+    static_assert(detail::is_real<T>::value, "float or double");
+    with_device_(w, (uint64_t) n * sizeof(T), true, true, [&](void* d) {
+        if (std::is_same<T, float>::value) detail::check(rbx_weights_to_cdf_f32(n, (float*) d, (float) error_if_below, current_stream()), "weights_to_cdf");
+        else                               detail::check(rbx_weights_to_cdf_f64(n, (double*) d, (double) error_if_below, current_stream()), "weights_to_cdf");
+    });
+}
+template <typename TF, typename RNG = r123::Philox4x32>
+inline RNGState<RNG> sample_indices_iid(int64_t n, TF* cdf, int64_t k, int64_t* samples, RNGState<RNG> state) {   // util.hh:284-305
+    static_assert(detail::is_real<TF>::value, "float or double");
+    RNGState<RNG> out = state;
+    with_device_(cdf, (uint64_t) n * sizeof(TF), true, false, [&](void* dc) {
+        with_device_(samples, (uint64_t) k * 8, false, true, [&](void* ds) {
+            if (std::is_same<TF, float>::value)
+                detail::check(rbx_sample_indices_iid_f32(n, (const float*) dc, k, (int64_t*) ds, state.counter, state.key, out.counter, current_stream()), "sample_indices_iid");
+            else
+                detail::check(rbx_sample_indices_iid_f64(n, (const double*) dc, k, (int64_t*) ds, state.counter, state.key, out.counter, current_stream()), "sample_indices_iid");
+        });
+    });
+    return out;
+}
+template <typename RNG = r123::Philox4x32>
+inline RNGState<RNG> sample_indices_iid_uniform(int64_t n, int64_t k, int64_t* samples, RNGState<RNG> state) {     // util.hh:311-334
+    RNGState<RNG> out = state;
+    with_device_(samples, (uint64_t) k * 8, false, true, [&](void* ds) {
+        detail::check(rbx_sample_indices_iid_uniform(n, k, (int64_t*) ds, state.counter, state.key, out.counter, current_stream()), "sample_indices_iid_uniform");
+    });
+    return out;
 }
 }  // namespace util
 

@@ -26,6 +26,9 @@ int orc_sketch_sparseop_f64(char, char, char, char, int64_t, int64_t, int64_t, d
 int orc_sketch_sparsedata_f64(char, char, char, char, int64_t, int64_t, int64_t, double, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
                               int64_t, int64_t, char, int64_t, int64_t, int64_t, const double*, const int64_t*, const int64_t*, int64_t, int64_t,
                               double, double*, int64_t);
+int orc_sample_indices_iid_uniform(int64_t, int64_t, int64_t*, const uint32_t*, const uint32_t*, uint32_t*);
+int orc_sample_indices_iid_f64(int64_t, const double*, int64_t, int64_t*, const uint32_t*, const uint32_t*, uint32_t*);
+int orc_weights_to_cdf_f64(int64_t, double*, double);
 }
 
 using namespace RandBLAS;
@@ -190,6 +193,30 @@ static void test_sketch_sparse() {
     CHECK(max_rel(B, W) < 1e-13);
 }
 
+static void test_index_sampling() {
+    // util::weights_to_cdf / sample_indices_iid / sample_indices_iid_uniform (util.hh:257-334), host pointers
+    const int64_t n = 500, k = 1001;
+    std::vector<double> w = randmat(n, 4), cdf(n);
+    for (auto& v : w) v = std::abs(v);
+    cdf = w;
+    util::weights_to_cdf(n, w.data());
+    CHECK(orc_weights_to_cdf_f64(n, cdf.data(), -std::numeric_limits<double>::epsilon()) == 0);
+    CHECK(bits_equal(w, cdf));
+    RNGState<> st(11);
+    std::vector<int64_t> got(k), want(k);
+    uint32_t next[4];
+    RNGState<> out = util::sample_indices_iid(n, w.data(), k, got.data(), st);
+    orc_sample_indices_iid_f64(n, cdf.data(), k, want.data(), st.counter, st.key, next);
+    CHECK(got == want && std::memcmp(out.counter, next, 16) == 0);
+    out = util::sample_indices_iid_uniform(n, k, got.data(), st);
+    orc_sample_indices_iid_uniform(n, k, want.data(), st.counter, st.key, next);
+    CHECK(got == want && std::memcmp(out.counter, next, 16) == 0);
+    bool threw = false;
+    std::vector<double> bad = { 0.5, -0.1, 0.5 };
+    try { util::weights_to_cdf(3, bad.data()); } catch (const Error&) { threw = true; }
+    CHECK(threw);
+}
+
 int main() {
     if (rbx_device_count() < 1) { std::printf("no CUDA device: the product path has no CPU fallback\n"); return 77; }
     test_fill_dense();
@@ -197,6 +224,7 @@ int main() {
     test_sketch_dense();
     test_sketch_sparseop();
     test_sketch_sparse();
+    test_index_sampling();
     std::printf(failures ? "FAILED (%d)\n" : "OK\n", failures);
     return failures ? 1 : 0;
 }
