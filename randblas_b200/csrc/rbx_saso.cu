@@ -88,8 +88,8 @@ __device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* ou
 // Slot q = bucket * NS + s owns rows bucket*64 + h*NS + s, h < HALVES (the half-warps of a double-precision warp work on
 // different rows). n(q) = max over h of the row's entry count in this chunk. Outputs, per chunk:
 //   rec[chunk * rec_stride + (q * HALVES + h) * 4 ..]   one 16-byte record per (slot, half): the row's first SASO_NU
-//        codes (zero code where it has fewer) and n(q). The record of a bucket's slot 0 also carries, above bit 12, where
-//        the bucket's tail codes start inside its row block's region, and in bit 31 "not in the region";
+//        codes (zero code where it has fewer) and the slot's tail count max(n(q) - SASO_NU, 0). The record of a bucket's
+//        slot 0 also carries, above bit 12, where the bucket's tail codes start inside its row block's region, and in bit 31 "not in the region";
 //   stream[chunk * stream_stride + (rb * cap + ...) * HALVES + h]   region of row block rb: the tails (elements SASO_NU ..
 //        n(q)-1, HALVES codes per element, the shorter row padded with the zero code) of its buckets, bucket after bucket,
 //        as long as they fit in cap elements. The main kernel copies the region into the ring stage;
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
                                                                int64_t M, int64_t K, int CK, int nbuckets, int nrb, int cols_contig, int cap,
                                                                uint32_t* __restrict__ stream, int stream_stride,
                                                                uint32_t* __restrict__ rec, int rec_stride,
-                                                               uint32_t* __restrict__ ws, int ws_stride) {
+                                                               uint32_t* __restrict__ ws, int ws_stride, int* __restrict__ spill_flag) {
     constexpr int NS = SASO_RW / HALVES;
     extern __shared__ uint32_t sh32[];
     __shared__ uint32_t wtot[SASO_WARPS];
@@ -178,6 +178,7 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     const uint32_t region_words = (uint32_t)(nrb * cap * HALVES);
     for (uint32_t e = t; e < region_words; e += SASO_THREADS) so[e] = zero_code;
     if (any_spill) {
+        if (t == 0) *spill_flag = 1;
         const uint32_t used = slotoff[nslots] * HALVES;
         for (uint32_t e = t; e < used; e += SASO_THREADS) so[region_words + e] = zero_code;
     }
@@ -195,7 +196,7 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
             const uint32_t b_start = slotoff[b * NS] - rb_base[rb], b_end = slotoff[(b + 1) * NS] - rb_base[rb];
             const bool fits = b_end <= (uint32_t) cap;
             tails = fits ? so + ((size_t) rb * cap + (slotoff[q] - rb_base[rb])) * HALVES : so + region_words + (size_t) slotoff[q] * HALVES;
-            w = n | (s == 0 ? ((fits ? b_start << 12 : SASO_SIGN)) : 0u);
+            w = tailcnt[q] | (s == 0 ? ((fits ? b_start << 12 : SASO_SIGN)) : 0u);
         }
 #pragma unroll
         for (int h = 0; h < HALVES; ++h) {
@@ -222,6 +223,7 @@ struct SasoArgs {
     T alpha, beta;
     T* C; int64_t sc_i, sc_j;
     T* partial;                                        // [msplit][M][njb * W] when msplit > 1
+    const int* spill_flag;                             // set by the prep kernel: some tail codes are outside the regions
 };
 
 // asynchronous global->shared copies; bytes beyond src_bytes are zero-filled (ragged edges)
@@ -269,19 +271,20 @@ __device__ __forceinline__ double apply_sign(unsigned long long bits, uint32_t c
 __device__ __forceinline__ float apply_sign(uint32_t bits, uint32_t code) { return __uint_as_float(bits ^ (code & SASO_SIGN)); }
 
 // slots [0, NS) of this warp: acc[s] += sum of the gathered (signed) A values of its elements.
-// recs: shared address of this lane's first 16-byte slot record; region: this lane's first code of the row block's tail
-// region in the stage; spill / wsp: where the tails are in global memory when the bucket's did not fit in the region;
-// lanebase: shared address of this lane's column in row 0 of the stage's A chunk. Address of an element =
-// lanebase + (code << log2(sizeof(T))); the shift drops the sign bit.
+// recs: shared address of this lane's first 16-byte slot record; region_s: shared address of this lane's first code of the
+// row block's tail region in the stage; spill / wsp: where the tails are in global memory when the bucket's did not fit in
+// the region (SPILL variant only); lanebase: shared address of this lane's column in row 0 of the stage's A chunk.
+// Address of an element = lanebase + (code << log2(sizeof(T))); the shift drops the sign bit.
 // The walk goes G slots at a time: their records, then all of their gathers, are in flight together (4 warps per
-// scheduler cannot hide a record -> gather -> add chain per slot); the tails follow, one (rare) loop per slot.
-template <typename T, int NS, int HALVES>
-__device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, const uint32_t* region, const uint32_t* spill, const uint32_t* wsp,
+// scheduler cannot hide a record -> gather -> add chain per slot); the tails follow, one short loop per slot.
+template <typename T, int NS, int HALVES, bool SPILL>
+__device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, uint32_t region_s, const uint32_t* spill, const uint32_t* wsp,
                                              uint32_t lanebase, uint32_t zero_code) {
     constexpr int SH = sizeof(T) == 8 ? 3 : 2;
     constexpr int G = SASO_GROUP;
     typedef typename RawBits<T>::type raw_t;
-    const uint32_t* tp = region;
+    const uint32_t* tp = spill;      // SPILL: generic pointer to the bucket's tail codes (the stage's region or global memory)
+    uint32_t tps = region_s;         // !SPILL: their shared-memory address
 #pragma unroll
     for (int g = 0; g < NS; g += G) {
         uint32_t c[G][4];
@@ -292,7 +295,10 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, const 
         if (g == 0) {
             const uint32_t w = c[0][3];
             c[0][3] = w & 0xfffu;
-            tp = (w & SASO_SIGN) ? spill + (size_t) __ldg(wsp) * HALVES : region + ((w >> 12) & 0x7ffffu) * HALVES;
+            const uint32_t off = ((w >> 12) & 0x7ffffu) * (uint32_t)(HALVES * 4);
+            if (SPILL) tp = (w & SASO_SIGN) ? spill + (size_t) __ldg(wsp) * HALVES
+                                            : reinterpret_cast<const uint32_t*>(__cvta_shared_to_generic(region_s + off));
+            else tps = region_s + off;
         }
         raw_t v[G][SASO_NU];
 #pragma unroll
@@ -313,15 +319,28 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, const 
         uint32_t any = 0;
 #pragma unroll
         for (int j = 0; j < G; ++j) any |= c[j][3];
-        if (any > (uint32_t) SASO_NU) {             // some slot of the group has more than SASO_NU elements
+        if (any != 0) {                             // some slot of the group has more than SASO_NU elements
 #pragma unroll
             for (int j = 0; j < G; ++j) {
+                if (SPILL) {
 #pragma unroll 1
-                for (uint32_t i = SASO_NU; i < c[j][3]; ++i) {
-                    uint32_t code;
-                    asm volatile("ld.b32 %0, [%1];" : "=r"(code) : "l"(tp));     // generic: the stage's region or global memory
-                    tp += HALVES;
-                    acc[g + j] += lds_signed<T>(lanebase + (code << SH), code);
+                    for (uint32_t i = 0; i < c[j][3]; ++i) {
+                        uint32_t code;
+                        asm volatile("ld.b32 %0, [%1];" : "=r"(code) : "l"(tp));
+                        tp += HALVES;
+                        acc[g + j] += lds_signed<T>(lanebase + (code << SH), code);
+                    }
+                } else {
+                    const uint32_t end = tps + c[j][3] * (uint32_t)(HALVES * 4);
+#pragma unroll 1
+                    for (; tps != end; tps += HALVES * 4) {
+                        uint32_t code;
+                        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(code) : "r"(tps));
+                        raw_t raw;
+                        if (sizeof(T) == 8) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(*reinterpret_cast<unsigned long long*>(&raw)) : "r"(lanebase + (code << SH)));
+                        else asm volatile("ld.shared.b32 %0, [%1];" : "=r"(*reinterpret_cast<uint32_t*>(&raw)) : "r"(lanebase + (code << SH)));
+                        acc[g + j] += apply_sign(raw, code);
+                    }
                 }
             }
         }
@@ -333,8 +352,13 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, const 
 // cp.async, pitch 128); column-contiguous data is copied element by element (8 / 4-byte cp.async, lanes run down a
 // column) with a pitch of 128 bytes + one element, which spreads that transposing write over all banks while the gather
 // (lanes along a row) stays contiguous.
-template <typename T, bool COLS_CONTIG>
+// SPILL: the variant that can read tail codes from global memory. The prep kernel raises *a.spill_flag when any bucket's
+// tails did not fit in its region (far tail of the distribution); both variants are launched and the one the flag does
+// not select returns at once. Keeping the global-memory path out of the common variant keeps its unrolled walk small:
+// unexecuted code inside that loop cost 2.5 % of the kernel time (instruction cache).
+template <typename T, bool COLS_CONTIG, bool SPILL>
 __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoArgs<T> a) {
+    if ((__ldg(a.spill_flag) != 0) != SPILL) return;
     constexpr int W = SASO_ROWB / (int) sizeof(T);     // columns per CTA: 16 doubles / 32 floats
     constexpr int HALVES = 32 / W;                     // entries per warp instruction: 2 / 1
     constexpr int NS = SASO_RW / HALVES;               // accumulators per lane: 32 doubles / 64 floats
@@ -440,10 +464,9 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
         cp_async_commit();
         if (active && a.dbg_skip != 1) {
             const uint32_t st = smem0 + (uint32_t)(it % NST) * stage_bytes;
-            const uint8_t* st8 = smem + (size_t)(it % NST) * stage_bytes;
             const uint32_t recs = st + az_bytes + (uint32_t)((warp * NS * HALVES + sub) * 16);
-            const uint32_t* region = reinterpret_cast<const uint32_t*>(st8 + az_bytes + REC_BYTES) + sub;
-            saso_consume<T, NS, HALVES>(acc, recs, region, spill + (size_t) ch * a.stream_stride, a.ws + (size_t) ch * a.ws_stride + bucket,
+            const uint32_t region = st + (uint32_t)(az_bytes + REC_BYTES + sub * 4);
+            saso_consume<T, NS, HALVES, SPILL>(acc, recs, region, spill + (size_t) ch * a.stream_stride, a.ws + (size_t) ch * a.ws_stride + bucket,
                                         st + lx, zero_code);
         }
     }
@@ -540,25 +563,28 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     const int stream_stride = ((nrb * cap + E) * HALVES + 3) & ~3;               // tail codes per chunk: regions, then spill
     const int rec_stride = nrb * SASO_WARPS * NS * HALVES * 4;                  // record words per chunk
     const int ws_stride = (nbuckets + 1 + 3) & ~3;
-    uint32_t* codes = nullptr; uint32_t* rec = nullptr; uint32_t* ws = nullptr; T* partial = nullptr;
+    uint32_t* codes = nullptr; uint32_t* rec = nullptr; uint32_t* ws = nullptr; T* partial = nullptr; int* flag = nullptr;
     const size_t Np = (size_t) njb * W;
     const size_t part_bytes = msplit > 1 ? (size_t) msplit * M * Np * sizeof(T) : 0;
     if (ws_alloc(&codes, (size_t) nchunks * stream_stride * 4, stream) != cudaSuccess ||
         ws_alloc(&rec, (size_t) nchunks * rec_stride * 4, stream) != cudaSuccess ||
         ws_alloc(&ws, (size_t) nchunks * ws_stride * 4, stream) != cudaSuccess ||
+        ws_alloc(&flag, sizeof(int), stream) != cudaSuccess ||
         (part_bytes && ws_alloc(&partial, part_bytes, stream) != cudaSuccess)) {
         cudaGetLastError();
         if (codes) cudaFreeAsync(codes, stream);
         if (rec) cudaFreeAsync(rec, stream);
         if (ws) cudaFreeAsync(ws, stream);
+        if (flag) cudaFreeAsync(flag, stream);
         return RBX_ERR_ALLOC;
     }
     int rc = RBX_OK;
-    {
+    if (cudaMemsetAsync(flag, 0, sizeof(int), stream) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    if (rc == RBX_OK) {
         auto kern = vec_nnz <= 8 ? saso_prep_kernel<8, HALVES> : saso_prep_kernel<32, HALVES>;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) prep_smem);
         kern<<<nchunks, SASO_THREADS, prep_smem, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, CK, nbuckets, nrb, cols_contig ? 1 : 0, cap,
-                                                           codes, stream_stride, rec, rec_stride, ws, ws_stride);
+                                                           codes, stream_stride, rec, rec_stride, ws, ws_stride, flag);
         count_launch();
         rc = check_launch("saso_prep_kernel");
     }
@@ -570,13 +596,16 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         a.CK = CK; a.cap = cap;
         a.nbuckets = nbuckets; a.njb = njb; a.nrb = nrb; a.msplit = msplit; a.nchunks = nchunks;
         a.dbg_skip = getenv("RBX_SASO_SKIP") ? atoi(getenv("RBX_SASO_SKIP")) : 0;
-        a.M = M; a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial;
+        a.M = M; a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial; a.spill_flag = flag;
         const unsigned grid = (unsigned)(njb * msplit * nrb);
         const size_t smem = nst * stage;
-        auto tile = cols_contig ? saso_tile_kernel<T, true> : saso_tile_kernel<T, false>;
+        auto tile = cols_contig ? saso_tile_kernel<T, true, false> : saso_tile_kernel<T, false, false>;
+        auto tile_spill = cols_contig ? saso_tile_kernel<T, true, true> : saso_tile_kernel<T, false, true>;
         cudaFuncSetAttribute(tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        cudaFuncSetAttribute(tile_spill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         tile<<<grid, SASO_THREADS, smem, stream>>>(a);
-        count_launch();
+        tile_spill<<<grid, SASO_THREADS, smem, stream>>>(a);      // returns at once unless the prep kernel raised the flag
+        count_launch(); count_launch();
         rc = check_launch("saso_tile_kernel");
         if (rc == RBX_OK && msplit > 1) {
             int64_t blocks = (M * N + 255) / 256;
@@ -586,7 +615,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
             rc = check_launch("saso_reduce_kernel");
         }
     }
-    cudaFreeAsync(codes, stream); cudaFreeAsync(rec, stream); cudaFreeAsync(ws, stream);
+    cudaFreeAsync(codes, stream); cudaFreeAsync(rec, stream); cudaFreeAsync(ws, stream); cudaFreeAsync(flag, stream);
     if (partial) cudaFreeAsync(partial, stream);
     return rc;
 }
