@@ -58,6 +58,23 @@ constexpr int SASO_NU = SASO_NU_VAL;          // codes held by a slot record; th
 #define SASO_GROUP 4      // slots whose records and gathers are in flight together
 #endif
 static_assert(SASO_NU == 3, "the 16-byte slot record holds three codes and the count");
+// SASO_PRODUCER = 1: a 17th warp issues every cp.async of the ring and the 16 consumer warps are coupled to it only through
+// two mbarriers per stage (full: the copies have landed; empty: all consumer warps are done with the stage), so a warp that
+// finishes its slots early starts on the next chunk instead of waiting at a CTA-wide barrier for the slowest warp.
+#ifndef SASO_PRODUCER
+#define SASO_PRODUCER 2
+#endif
+// SASO_PRODUCER = 2: a whole producer warp group (registers are allocated to groups of four warps anyway), which hands most
+// of its registers to the consumers with setmaxnreg.
+// The CTA's register pool is what it was launched with: 640 threads x 96. 16 consumer warps x 112 + 4 producer warps x 24
+// fits; 120 does not and the allocation would spin forever.
+#ifndef SASO_CONS_REGS
+#define SASO_CONS_REGS 112
+#endif
+static_assert(SASO_PRODUCER != 2 || SASO_WARPS * SASO_CONS_REGS + 4 * 24 <= (SASO_WARPS + 4) * 96, "setmaxnreg.inc beyond the CTA's register pool deadlocks");
+constexpr int SASO_PROD_WARPS = SASO_PRODUCER == 2 ? 4 : (SASO_PRODUCER ? 1 : 0);
+constexpr int SASO_TILE_THREADS = SASO_THREADS + SASO_PROD_WARPS * 32;
+constexpr int SASO_LOAD_THREADS = SASO_PRODUCER ? SASO_PROD_WARPS * 32 : SASO_THREADS;    // threads that share the copies of one chunk
 
 // exclusive scan of in[0..n) into out[0..n], out[n] = total; all SASO_THREADS threads of the block call it
 __device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* out, int n, uint32_t* wtot) {
@@ -357,7 +374,7 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, uint32
 // not select returns at once. Keeping the global-memory path out of the common variant keeps its unrolled walk small:
 // unexecuted code inside that loop cost 2.5 % of the kernel time (instruction cache).
 template <typename T, bool COLS_CONTIG, bool SPILL>
-__global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoArgs<T> a) {
+__global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const SasoArgs<T> a) {
     if ((__ldg(a.spill_flag) != 0) != SPILL) return;
     constexpr int W = SASO_ROWB / (int) sizeof(T);     // columns per CTA: 16 doubles / 32 floats
     constexpr int HALVES = 32 / W;                     // entries per warp instruction: 2 / 1
@@ -389,7 +406,7 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     const int ce = COLS_CONTIG ? a.nchunks : ((cb + per < a.nchunks) ? cb + per : a.nchunks);
     const int64_t j0 = (int64_t) jb * W;
     const int bucket = rb * SASO_WARPS + warp;         // warp owns rows [bucket*64, bucket*64+64) of the window
-    const bool active = bucket < a.nbuckets;
+    const bool active = warp < SASO_WARPS && bucket < a.nbuckets;
 
     constexpr int NST = COLS_CONTIG ? SASO_NST_COLS : SASO_NST_ROWS;
     if (tid < NST * (SASO_ROWB / 8))                   // the zero rows of the stages
@@ -399,17 +416,20 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     // memory: the copies of the next chunk are issued without waiting for anything.
     // Tiles that touch neither edge of A take the copy loops without per-piece bounds arithmetic.
     const bool cols_inside = j0 + W <= a.N;
+    constexpr int LT = SASO_LOAD_THREADS;
+    const int lt = SASO_PRODUCER ? tid - SASO_THREADS : tid;
     auto load_async = [&](int ch, int s) {
         const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
         const bool inside = cols_inside && (int64_t)(ch + 1) * CK <= a.K;
         if (!COLS_CONTIG) {
             if (inside) {
-                const T* src = a.X + ((int64_t) ch * CK + (tid >> 3)) * a.sx_l + j0 + (tid & 7) * EP;
-                const int64_t step = (int64_t)(SASO_THREADS / 8) * a.sx_l;
-                uint32_t dst = st + tid * 16;
-                for (int i = 0; i < CK / (SASO_THREADS / 8); ++i) { cp_async16(dst, src, 16); dst += SASO_THREADS * 16; src += step; }
+                const T* src = a.X + ((int64_t) ch * CK + (lt >> 3)) * a.sx_l + j0 + (lt & 7) * EP;
+                const int64_t step = (int64_t)(LT / 8) * a.sx_l;
+                uint32_t dst = st + lt * 16;
+#pragma unroll 8
+                for (int i = 0; i < CK / (LT / 8); ++i) { cp_async16(dst, src, 16); dst += LT * 16; src += step; }
             } else {
-                for (int p = tid; p < CK * 8; p += SASO_THREADS) {
+                for (int p = lt; p < CK * 8; p += LT) {
                     const int row = p >> 3, q = p & 7;
                     const int64_t l = (int64_t) ch * CK + row, col = j0 + (int64_t) q * EP;
                     int64_t nb = (l < a.K) ? (a.N - col) * (int64_t) sizeof(T) : 0;
@@ -419,7 +439,7 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
                 }
             }
         } else {
-            for (int rr = tid; rr < CK; rr += SASO_THREADS) {
+            for (int rr = lt; rr < CK; rr += LT) {
                 const int64_t l = (int64_t) ch * CK + rr;
                 const uint32_t row = st + rr * PITCH;
                 if (inside) {
@@ -437,17 +457,11 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
             }
         }
         const uint8_t* rsrc = reinterpret_cast<const uint8_t*>(a.rec + (size_t) ch * a.rec_stride) + (size_t) rb * REC_BYTES;
-        for (int p = tid; p < REC_BYTES / 16; p += SASO_THREADS) cp_async16(st + az_bytes + p * 16, rsrc + p * 16, 16);
+        for (int p = lt; p < REC_BYTES / 16; p += LT) cp_async16(st + az_bytes + p * 16, rsrc + p * 16, 16);
         const uint8_t* tsrc = reinterpret_cast<const uint8_t*>(a.stream + (size_t) ch * a.stream_stride) + (size_t) rb * tail_bytes;
         // the threads that were idle (column-contiguous) or last (row-contiguous) in the A copy take the tail region
-        for (int p = SASO_THREADS - 1 - tid; p < tail_bytes / 16; p += SASO_THREADS) cp_async16(st + az_bytes + REC_BYTES + p * 16, tsrc + p * 16, 16);
+        for (int p = LT - 1 - lt; p < tail_bytes / 16; p += LT) cp_async16(st + az_bytes + REC_BYTES + p * 16, tsrc + p * 16, 16);
     };
-
-    constexpr int DIST = NST - 1;                      // prefetch distance in chunks
-    for (int s = 0; s < DIST; ++s) {
-        if (cb + s * cstep < ce) load_async(cb + s * cstep, s);
-        cp_async_commit();
-    }
 
     T acc[NS];
 #pragma unroll
@@ -456,6 +470,50 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
     const uint32_t zero_code = (uint32_t) CK * (uint32_t)(PITCH / (int) sizeof(T));
     const uint32_t* spill = a.stream + (size_t) a.nrb * a.cap * HALVES + sub;
 
+#if SASO_PRODUCER
+    __shared__ __align__(8) uint64_t full_bar[NST], empty_bar[NST];
+    if (tid == 0) {
+        for (int s = 0; s < NST; ++s) { mbar_init(&full_bar[s], SASO_LOAD_THREADS); mbar_init(&empty_bar[s], SASO_WARPS); }
+        fence_mbar_init();
+    }
+    __syncthreads();                                    // barriers and zero rows are in place
+    if (warp >= SASO_WARPS) {
+        // ---- producer warp(s): every copy of the ring ----
+#if SASO_PRODUCER == 2
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+#endif
+        for (int ch = cb, it = 0; ch < ce; ch += cstep, ++it) {
+            const int s = it % NST, u = it / NST;
+            if (u > 0) mbar_wait(&empty_bar[s], (uint32_t)(u - 1) & 1u);
+            load_async(ch, s);
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(smem_u32(&full_bar[s])) : "memory");
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+        return;
+    }
+#if SASO_PRODUCER == 2
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" :: "n"(SASO_CONS_REGS));
+#endif
+    for (int ch = cb, it = 0; ch < ce; ch += cstep, ++it) {
+        const int s = it % NST;
+        mbar_wait(&full_bar[s], (uint32_t)(it / NST) & 1u);
+        if (active && a.dbg_skip != 1) {
+            const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
+            const uint32_t recs = st + az_bytes + (uint32_t)((warp * NS * HALVES + sub) * 16);
+            const uint32_t region = st + (uint32_t)(az_bytes + REC_BYTES + sub * 4);
+            saso_consume<T, NS, HALVES, SPILL>(acc, recs, region, spill + (size_t) ch * a.stream_stride, a.ws + (size_t) ch * a.ws_stride + bucket,
+                                        st + lx, zero_code);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
+    }
+#else
+    constexpr int DIST = NST - 1;                      // prefetch distance in chunks
+    for (int s = 0; s < DIST; ++s) {
+        if (cb + s * cstep < ce) load_async(cb + s * cstep, s);
+        cp_async_commit();
+    }
     for (int ch = cb, it = 0; ch < ce; ch += cstep, ++it) {
         cp_async_wait<DIST - 1>();
         __syncthreads();                                // chunk `it` has landed; everyone is done with chunk it-1
@@ -471,6 +529,7 @@ __global__ void __launch_bounds__(SASO_THREADS, 1) saso_tile_kernel(const SasoAr
         }
     }
     cp_async_wait<0>();
+#endif
     if (active) {
         const int64_t col = j0 + jl;
 #pragma unroll
@@ -603,8 +662,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         auto tile_spill = cols_contig ? saso_tile_kernel<T, true, true> : saso_tile_kernel<T, false, true>;
         cudaFuncSetAttribute(tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         cudaFuncSetAttribute(tile_spill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        tile<<<grid, SASO_THREADS, smem, stream>>>(a);
-        tile_spill<<<grid, SASO_THREADS, smem, stream>>>(a);      // returns at once unless the prep kernel raised the flag
+        tile<<<grid, SASO_TILE_THREADS, smem, stream>>>(a);
+        tile_spill<<<grid, SASO_TILE_THREADS, smem, stream>>>(a);      // returns at once unless the prep kernel raised the flag
         count_launch(); count_launch();
         rc = check_launch("saso_tile_kernel");
         if (rc == RBX_OK && msplit > 1) {
