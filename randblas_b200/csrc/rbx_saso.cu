@@ -21,7 +21,15 @@
 //     than its partner is padded with a code that points at a zero row of the ring;
 //   * the row blocks (d / 1024) of one column segment are adjacent CTAs and re-read the A chunk through L2, so HBM
 //     sees each byte of A once.
-// Rejected after measurement: TMA boxes for the A chunk (256-byte box rows are TMA row-rate bound, ~28 cycles/row),
+//   * warp roles: 16 consumer warps walk the slots; a producer warp group issues every cp.async of the ring and is coupled
+//     to them only through two mbarriers per stage (full / empty), so a warp that finishes its slots early moves on to
+//     the next chunk instead of waiting at a CTA-wide barrier for the slowest of the 16 (that barrier cost 20 %);
+//     setmaxnreg gives the producers' registers to the consumers.
+// Rejected after measurement: predicated "first tail element of every slot in flight together" rounds before the serial
+// tail loops (1 / 2 / 3 rounds: +4 / +9 / +20 % time: the kernel is bound by issue slots and shared-memory wavefronts, not
+// by the latency of the tail chain), a pause in the producers' polling loop (no change), carrying the gather predicate to
+// the add instead of zeroing the value register (ptxas spills ~1 KB per thread),
+// TMA boxes for the A chunk (256-byte box rows are TMA row-rate bound, ~28 cycles/row),
 // cluster multicast (73 cycles/row), register tiles selected with brx.idx (~45 issue slots per select), B tile in
 // shared memory with read-modify-write (latency bound at 16 warps/SM, 24 B of shared-memory traffic per update).
 #include <cmath>
@@ -44,6 +52,9 @@ constexpr int SASO_THREADS = SASO_WARPS * 32;
 #endif
 #ifndef SASO_CK_MAX
 #define SASO_CK_MAX 704         // longest chunk (a multiple of 64); the ring stages must fit in shared memory
+#endif
+#ifndef SASO_CK_MAX_COLS
+#define SASO_CK_MAX_COLS 576    // column-contiguous data (measured at C2: 704 -> 11.1 ms, 576 -> 10.8 ms, 512 -> 11.0 ms)
 #endif
 #ifndef SASO_ALWAYS
 #define SASO_ALWAYS 1         // leading gathers of a slot that are not predicated (a row has a first entry 86 % of the time at C2)
@@ -596,7 +607,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     int CK = 0, cap = 0;
     const size_t nst = cols_contig ? SASO_NST_COLS : SASO_NST_ROWS;
     size_t stage = 0;
-    for (int ck = SASO_CK_MAX; ck >= 64; ck -= (cols_contig ? 16 : 64)) {
+    for (int ck = cols_contig ? SASO_CK_MAX_COLS : SASO_CK_MAX; ck >= 64; ck -= (cols_contig ? 16 : 64)) {
         if ((size_t) ck * vec_nnz * 10 + (size_t)(2 * nbuckets * SASO_RW + 3 * nbuckets * NS + 2) * 4 + 16 > SMEM_MAX) continue;   // the prep kernel's sort
         // tail elements of one row block per chunk: mean + 8 sigma (Poisson tails; sigma^2 < 2 * mean); a bucket that
         // does not fit reads its tails from global memory
