@@ -83,6 +83,10 @@ static_assert(SASO_NU == 3, "the 16-byte slot record holds three codes and the c
 #define SASO_CONS_REGS 112
 #endif
 static_assert(SASO_PRODUCER != 2 || SASO_WARPS * SASO_CONS_REGS + 4 * 24 <= (SASO_WARPS + 4) * 96, "setmaxnreg.inc beyond the CTA's register pool deadlocks");
+#ifndef SASO_BULK_META
+#define SASO_BULK_META 1          // 1: with row-contiguous data the slot records and tail region of a chunk arrive by two bulk copies (TMA)
+                                  // instead of 16-byte cp.async (C2: 9.40 -> 9.23 ms; column-contiguous data lost 3 % with it and keeps cp.async)
+#endif
 constexpr int SASO_PROD_WARPS = SASO_PRODUCER == 2 ? 4 : (SASO_PRODUCER ? 1 : 0);
 constexpr int SASO_TILE_THREADS = SASO_THREADS + SASO_PROD_WARPS * 32;
 constexpr int SASO_LOAD_THREADS = SASO_PRODUCER ? SASO_PROD_WARPS * 32 : SASO_THREADS;    // threads that share the copies of one chunk
@@ -429,6 +433,10 @@ __global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const S
     const bool cols_inside = j0 + W <= a.N;
     constexpr int LT = SASO_LOAD_THREADS;
     const int lt = SASO_PRODUCER ? tid - SASO_THREADS : tid;
+    constexpr bool BULK_META = SASO_PRODUCER && SASO_BULK_META && !COLS_CONTIG;
+#if SASO_PRODUCER
+    __shared__ __align__(8) uint64_t full_bar[NST], empty_bar[NST];
+#endif
     auto load_async = [&](int ch, int s) {
         const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
         const bool inside = cols_inside && (int64_t)(ch + 1) * CK <= a.K;
@@ -468,10 +476,24 @@ __global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const S
             }
         }
         const uint8_t* rsrc = reinterpret_cast<const uint8_t*>(a.rec + (size_t) ch * a.rec_stride) + (size_t) rb * REC_BYTES;
-        for (int p = lt; p < REC_BYTES / 16; p += LT) cp_async16(st + az_bytes + p * 16, rsrc + p * 16, 16);
         const uint8_t* tsrc = reinterpret_cast<const uint8_t*>(a.stream + (size_t) ch * a.stream_stride) + (size_t) rb * tail_bytes;
-        // the threads that were idle (column-contiguous) or last (row-contiguous) in the A copy take the tail region
-        for (int p = LT - 1 - lt; p < tail_bytes / 16; p += LT) cp_async16(st + az_bytes + REC_BYTES + p * 16, tsrc + p * 16, 16);
+#if SASO_PRODUCER
+        if (BULK_META) {
+          if (lt == 0) {
+            mbar_expect_tx(&full_bar[s], (uint32_t)(REC_BYTES + tail_bytes));
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         :: "r"(st + az_bytes), "l"(rsrc), "r"((uint32_t) REC_BYTES), "r"(smem_u32(&full_bar[s])) : "memory");
+            if (tail_bytes > 0)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"(st + az_bytes + REC_BYTES), "l"(tsrc), "r"((uint32_t) tail_bytes), "r"(smem_u32(&full_bar[s])) : "memory");
+          }
+        } else
+#endif
+        {
+            for (int p = lt; p < REC_BYTES / 16; p += LT) cp_async16(st + az_bytes + p * 16, rsrc + p * 16, 16);
+            // the threads that were idle (column-contiguous) or last (row-contiguous) in the A copy take the tail region
+            for (int p = LT - 1 - lt; p < tail_bytes / 16; p += LT) cp_async16(st + az_bytes + REC_BYTES + p * 16, tsrc + p * 16, 16);
+        }
     };
 
     T acc[NS];
@@ -482,9 +504,8 @@ __global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const S
     const uint32_t* spill = a.stream + (size_t) a.nrb * a.cap * HALVES + sub;
 
 #if SASO_PRODUCER
-    __shared__ __align__(8) uint64_t full_bar[NST], empty_bar[NST];
     if (tid == 0) {
-        for (int s = 0; s < NST; ++s) { mbar_init(&full_bar[s], SASO_LOAD_THREADS); mbar_init(&empty_bar[s], SASO_WARPS); }
+        for (int s = 0; s < NST; ++s) { mbar_init(&full_bar[s], SASO_LOAD_THREADS + (BULK_META ? 1 : 0)); mbar_init(&empty_bar[s], SASO_WARPS); }
         fence_mbar_init();
     }
     __syncthreads();                                    // barriers and zero rows are in place
