@@ -42,13 +42,28 @@ template <> __device__ __forceinline__ void store4<double>(double* p, double a, 
 }
 
 // VEC: every block of every row is complete, unit column stride, and 4-element aligned in memory.
-template <typename T, char FAMILY, bool VEC>
+// LINEAR (with VEC): the window is whole parent rows stored back to back, so item k is counter k and float4 k -- the
+// whole-matrix fill (BASELINE config 3). The general walk's 64-bit (row, block) bookkeeping with its wrap correction is a
+// third of the uniform kernel's instructions; this loop has none of it.
+template <typename T, char FAMILY, bool VEC, bool LINEAR>
 __global__ void __launch_bounds__(256) fill_dense_kernel(T* __restrict__ out, const FillParams p, T scale, bool do_scale) {
     __shared__ double tab[32];
     if (FAMILY == 'G') { load_logf_tab(tab); __syncthreads(); }
 
     const int64_t tid = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= p.items) return;
+    if (LINEAR) {
+        double kl[14];
+        if (FAMILY == 'G') hoist_bm_consts(kl);
+        const Ctr128 base = ctr_add(p.ctr, (uint64_t)(p.r0 * p.W));
+        const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+        for (int64_t it = tid; it < p.items; it += stride) {
+            const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
+            store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, do_scale), cast_scale<T>(v.y, scale, do_scale),
+                      cast_scale<T>(v.z, scale, do_scale), cast_scale<T>(v.w, scale, do_scale));
+        }
+        return;
+    }
     // decompose the first item once, then walk with the precomputed (rows, blocks) stride
     int64_t i, b;
     if (p.rows_fastest) { b = tid / p.n_srows; i = tid - b * p.n_srows; }
@@ -108,9 +123,10 @@ int launch_fill_window(char family, int64_t n_cols_parent, T* out, int64_t n_sro
     else                { p.step_i = stride / p.nblk;  p.step_b = stride % p.nblk; }
     const T scale = (T) sqrt(3.0);   // (T)std::sqrt(3): dense_skops.hh:512
     dim3 g((unsigned) blocks), b(threads);
-#define RBX_FILL_LAUNCH(FAM, V) fill_dense_kernel<T, FAM, V><<<g, b, 0, stream>>>(out, p, scale, do_scale)
-    if (family == 'G') { if (vec) RBX_FILL_LAUNCH('G', true); else RBX_FILL_LAUNCH('G', false); }
-    else               { if (vec) RBX_FILL_LAUNCH('U', true); else RBX_FILL_LAUNCH('U', false); }
+    const bool linear = vec && !p.rows_fastest && c0 == 0 && p.nblk == p.W && n_scols == 4 * p.nblk && rs == n_scols;
+#define RBX_FILL_LAUNCH(FAM, V, L) fill_dense_kernel<T, FAM, V, L><<<g, b, 0, stream>>>(out, p, scale, do_scale)
+    if (family == 'G') { if (linear) RBX_FILL_LAUNCH('G', true, true); else if (vec) RBX_FILL_LAUNCH('G', true, false); else RBX_FILL_LAUNCH('G', false, false); }
+    else               { if (linear) RBX_FILL_LAUNCH('U', true, true); else if (vec) RBX_FILL_LAUNCH('U', true, false); else RBX_FILL_LAUNCH('U', false, false); }
 #undef RBX_FILL_LAUNCH
     count_launch();
     return check_launch("fill_dense_kernel");
