@@ -226,7 +226,7 @@ def main():
             traffic, traffic_src = tj["dram_bytes"], tj["source"]
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
                 "traffic_source": traffic_src, "peak_source": peak_src, "kernel_ms": k_ms, "algorithmic_bytes": alg_bytes,
-                "kernel": "saso_tile_kernel<double> (+ saso_prep_kernel and saso_reduce_kernel, < 1% of the step, inside the same events)"}
+                "kernel": "saso_tile_kernel<double> (+ saso_prep_kernel and saso_reduce_kernel, < 2% of the step, inside the same events)"}
 
     # end to end through the host-pointer C ABI (rank-local; N>1: every rank stages its own slab concurrently)
     e2e = None
