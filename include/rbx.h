@@ -28,6 +28,7 @@ extern "C" {
 #define RBX_ERR_NO_DEVICE  -3   /* no sm_100 device visible */
 #define RBX_ERR_ALLOC      -4   /* device workspace allocation failed */
 #define RBX_ERR_UNSUPPORTED -5  /* valid in the reference, not implemented on the device yet */
+#define RBX_ERR_TOO_LARGE  -6   /* beyond the fixed capacity of an allocation-free entry point (rbx_sketch_vector_noalloc) */
 
 const char* rbx_strerror(int code);
 const char* rbx_version(void);
@@ -133,6 +134,21 @@ int rbx_host_sketch_dense_f32(char side, char layout, char opS, char opA, int64_
 int rbx_host_sketch_dense_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
                               int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
                               int64_t ro_s, int64_t co_s, const double* A_host, int64_t lda, double beta, double* B_host, int64_t ldb);
+
+/* Allocation-free sketch_vector: y (d') = alpha * op(submat(S)) * x + beta * y for an implicit dense operator, dtype 'f'
+ * (float) or 'd' (double) for x / y / alpha / beta (alpha and beta are passed as double and narrowed); (d, m) are the dims of
+ * submat(S) BEFORE op, as in sketch_vector (skve.hh:152-176). Same kernels and results as rbx_sketch_dense_* with n = 1
+ * (gemv_rows / gemv_cols + gemv_reduce), but the per-chunk partial sums live in a file-scope `static __device__` array of
+ * 4 MiB instead of a stream-ordered allocation: the call issues no cudaMalloc / cudaMallocAsync / cudaFree (usable under
+ * CUDA graph capture and in loops that may not allocate). Limit: ceil(K / c) * M * sizeof(T) <= 4 MiB, where M / K are the
+ * output / contraction lengths and c = 1024 (generator rows along the output) or 64 (along the contraction); beyond it the
+ * call returns RBX_ERR_TOO_LARGE and prints the sizes. All calls on one GPU share the array: calls that overlap on the GPU
+ * (different streams) race; calls ordered on one stream are safe. Nothing in the array has to start at zero.
+ * NO COUNTERPART IN THE REFERENCE. */
+int rbx_sketch_vector_noalloc(char dtype, char opS, int64_t d, int64_t m, double alpha,
+                              int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                              int64_t ro_s, int64_t co_s, const void* x_dev, int64_t incx, double beta, void* y_dev, int64_t incy,
+                              void* stream);
 
 /* ---- sketching with a sparse operator: sparse::lskges / sparse::rskges, skge.hh:485-510 / 616-641 -- */
 /* Implicit operator: the SASO/LASO defined by (S_rows, S_cols, vec_nnz, major_axis, ctr, key) is regenerated on

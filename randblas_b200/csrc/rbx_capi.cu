@@ -227,6 +227,32 @@ static int sketch_dense(char side, char layout, char opS, char opA, int64_t p0, 
     return dispatch_dense_gemm<T>(g, (cudaStream_t) stream);
 }
 
+// sketch_vector without any allocation (rbx_sketch_vector_noalloc): the (RowMajor, n = 1) left sketch that
+// skve.hh:152-176 forwards to, with the partial sums of the GEMV kernels in a static device array
+template <typename T>
+static int sketch_vector_noalloc(char opS, int64_t d, int64_t m, T alpha, int64_t D_rows, int64_t D_cols, char family, char major_axis,
+                                 const uint32_t* ctr, const uint32_t* key, int64_t ro_s, int64_t co_s,
+                                 const T* x, int64_t incx, T beta, T* y, int64_t incy, void* stream) {
+    RBX_REQUIRE(is_op(opS) && d >= 0 && m >= 0 && incx >= 1 && incy >= 1);
+    const int64_t p0 = (opS == 'T') ? m : d, p2 = (opS == 'T') ? d : m;       // output / contraction length
+    SketchShape s;
+    RBX_TRY(sketch_shape('L', 'R', opS, 'N', p0, 1, p2, incx, incy, true, &s));
+    RBX_REQUIRE(ro_s >= 0 && co_s >= 0);
+    RBX_REQUIRE(D_rows >= s.rows_sub + ro_s && D_cols >= s.cols_sub + co_s);
+    GemmOperands<T> g{};
+    g.C = y; g.sc_i = s.sc_i; g.sc_j = s.sc_j;
+    g.X = x; g.sx_l = s.sx_l; g.sx_j = s.sx_j;
+    g.M = s.M; g.N = s.N; g.K = s.K;
+    g.alpha = alpha; g.beta = beta;
+    RBX_TRY(make_dense_window(D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s, &g.w));
+    g.l_on_cols = ((!s.s_trans) == (g.w.parent_is_S != 0)) ? 1 : 0;
+    g.Sx = nullptr;
+    RBX_NEED_DEVICE();
+    if (g.M == 0) return RBX_OK;
+    if (g.K == 0) return launch_scale_view<T>(y, g.M, 1, g.sc_i, g.sc_j, beta, (cudaStream_t) stream);
+    return launch_sketch_dense_gemv_static<T>(g, (cudaStream_t) stream);
+}
+
 // number of elements spanned by a (rows x cols) matrix in `layout` with leading dimension ld
 static inline size_t span_elems(char layout, int64_t rows, int64_t cols, int64_t ld) {
     if (rows <= 0 || cols <= 0) return 0;
@@ -509,6 +535,7 @@ const char* rbx_strerror(int code) {
         case RBX_ERR_NO_DEVICE: return "no sm_100 CUDA device visible (there is no CPU fallback)";
         case RBX_ERR_ALLOC: return "device workspace allocation failed";
         case RBX_ERR_UNSUPPORTED: return "case not implemented on the device";
+        case RBX_ERR_TOO_LARGE: return "problem exceeds the fixed scratch capacity of an allocation-free entry point";
         default: return "unknown rbx error code";
     }
 }
@@ -690,6 +717,18 @@ int rbx_weights_to_cdf_f64(int64_t n, double* w_dev, double error_if_below, void
     RBX_REQUIRE(n >= 0);
     RBX_NEED_DEVICE();
     return launch_weights_to_cdf<double>(n, w_dev, error_if_below, (cudaStream_t) stream);
+}
+
+int rbx_sketch_vector_noalloc(char dtype, char opS, int64_t d, int64_t m, double alpha, int64_t D_rows, int64_t D_cols, char family,
+                              char major_axis, const uint32_t ctr[4], const uint32_t key[2], int64_t ro_s, int64_t co_s,
+                              const void* x_dev, int64_t incx, double beta, void* y_dev, int64_t incy, void* stream) {
+    if (dtype == 'f')
+        return sketch_vector_noalloc<float>(opS, d, m, (float) alpha, D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s,
+                                            (const float*) x_dev, incx, (float) beta, (float*) y_dev, incy, stream);
+    if (dtype == 'd')
+        return sketch_vector_noalloc<double>(opS, d, m, alpha, D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s,
+                                             (const double*) x_dev, incx, beta, (double*) y_dev, incy, stream);
+    return RBX_ERR_ARG;
 }
 
 int rbx_malloc(void** dev_ptr, uint64_t bytes) {

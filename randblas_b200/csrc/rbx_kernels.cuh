@@ -42,6 +42,8 @@ struct GemmOperands {
 template <typename T> int launch_sketch_dense_simt(const GemmOperands<T>& g, cudaStream_t stream);
 // one right-hand side (sketch_vector): generator + dot product; RBX_ERR_UNSUPPORTED unless N == 1 and the operator is implicit
 template <typename T> int launch_sketch_dense_gemv(const GemmOperands<T>& g, cudaStream_t stream);
+// the same kernels with their partial sums in a static __device__ array (no allocation); RBX_ERR_TOO_LARGE beyond its size
+template <typename T> int launch_sketch_dense_gemv_static(const GemmOperands<T>& g, cudaStream_t stream);
 // tensor-core paths; return RBX_ERR_UNSUPPORTED when the shape/layout is outside their envelope
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream);
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream);

@@ -130,4 +130,72 @@ int launch_sketch_dense_gemv(const GemmOperands<T>& g, cudaStream_t stream) {
 template int launch_sketch_dense_gemv<float>(const GemmOperands<float>&, cudaStream_t);
 template int launch_sketch_dense_gemv<double>(const GemmOperands<double>&, cudaStream_t);
 
+// ---- allocation-free variant (rbx_sketch_vector_noalloc) -------------------------------------------------------------
+// Same two kernels, but the per-chunk partial sums live in a file-scope device array instead of a stream-ordered
+// allocation, for callers that may not allocate (CUDA graph capture, serving loops). Every GPU that loads the library holds
+// the array (GV_STATIC_BYTES) until exit. All calls share it: calls that overlap on the GPU (different streams) race.
+// Nothing in it has to start at zero -- the kernels write every (chunk, i) partial before the reduce kernel reads it -- so
+// the previous call's contents are simply overwritten.
+constexpr size_t GV_STATIC_BYTES = (size_t) 4 << 20;
+static __device__ __align__(256) unsigned char g_gv_scratch[GV_STATIC_BYTES];
+
+// In host code `g_gv_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device, with that device current, and cached.
+static void* gv_static_scratch() {
+    static void* ptr[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return nullptr; }
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_gv_scratch);
+        if (e != cudaSuccess) {
+            std::fprintf(stderr, "[rbx] cudaGetSymbolAddress(g_gv_scratch): %s\n", cudaGetErrorString(e));
+            cudaGetLastError();
+            return nullptr;
+        }
+        ptr[dev] = p;
+    }
+    return ptr[dev];
+}
+
+size_t sketch_vector_static_capacity() { return GV_STATIC_BYTES; }
+
+template <typename T>
+int launch_sketch_dense_gemv_static(const GemmOperands<T>& g, cudaStream_t stream) {
+    if (g.N != 1 || g.Sx != nullptr || g.M <= 0 || g.K <= 0) return RBX_ERR_UNSUPPORTED;
+    if (g.alpha == (T) 0) return launch_scale_view<T>(g.C, g.M, 1, g.sc_i, g.sc_j, g.beta, stream);      // one kernel, no workspace
+    GvArgs a;
+    a.w = g.w; a.M = g.M; a.K = g.K; a.sx = g.sx_l;
+    a.nchunks = g.l_on_cols ? (g.K + GV_LC - 1) / GV_LC : (g.K + GV_ROWS - 1) / GV_ROWS;
+    if (a.nchunks > 65535 || (g.M + 7) / 8 > 65535 ||
+        (double) a.nchunks * (double) g.M * (double) sizeof(T) > (double) GV_STATIC_BYTES) {
+        std::fprintf(stderr, "[rbx] rbx_sketch_vector_noalloc: %lld x %lld needs %lld partial sums of %d bytes; the static scratch holds %lld bytes\n",
+                     (long long) g.M, (long long) g.K, (long long)(a.nchunks * g.M), (int) sizeof(T), (long long) GV_STATIC_BYTES);
+        return RBX_ERR_TOO_LARGE;
+    }
+    T* partial = static_cast<T*>(gv_static_scratch());
+    if (!partial) return RBX_ERR_CUDA;
+    const bool G = g.w.family == 'G';
+    if (g.l_on_cols) {
+        dim3 grid((unsigned) a.nchunks, (unsigned)((g.M + 7) / 8));
+        if (G) gemv_rows_kernel<T, 'G'><<<grid, 256, 0, stream>>>(a, g.X, partial);
+        else   gemv_rows_kernel<T, 'U'><<<grid, 256, 0, stream>>>(a, g.X, partial);
+    } else {
+        const int64_t ncb = ((g.w.pc0 + g.M + 3) >> 2) - (g.w.pc0 >> 2);
+        dim3 grid((unsigned)((ncb + 255) / 256), (unsigned) a.nchunks);
+        if (G) gemv_cols_kernel<T, 'G'><<<grid, 256, 0, stream>>>(a, g.X, partial);
+        else   gemv_cols_kernel<T, 'U'><<<grid, 256, 0, stream>>>(a, g.X, partial);
+    }
+    count_launch();
+    int rc = check_launch("gemv kernel (static scratch)");
+    if (rc == RBX_OK) {
+        gemv_reduce_kernel<T><<<(unsigned)((g.M + 255) / 256), 256, 0, stream>>>(partial, a.nchunks, g.M, g.alpha, g.beta, g.C, g.sc_i);
+        count_launch();
+        rc = check_launch("gemv_reduce_kernel (static scratch)");
+    }
+    return rc;
+}
+template int launch_sketch_dense_gemv_static<float>(const GemmOperands<float>&, cudaStream_t);
+template int launch_sketch_dense_gemv_static<double>(const GemmOperands<double>&, cudaStream_t);
+
 }  // namespace rbx
