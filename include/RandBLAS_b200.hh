@@ -277,6 +277,11 @@ inline uint64_t span(blas::Layout l, int64_t rows, int64_t cols, int64_t ld) {
     if (rows <= 0 || cols <= 0) return 0;
     return l == blas::Layout::ColMajor ? (uint64_t) ld * (cols - 1) + rows : (uint64_t) ld * (rows - 1) + cols;
 }
+// B as a window of a larger host array: the device copy must start from the host's contents, because the whole span is copied
+// back and the reference never touches the elements between the columns / rows of the view
+inline bool padded(blas::Layout l, int64_t rows, int64_t cols, int64_t ld) {
+    return ld > (l == blas::Layout::ColMajor ? rows : cols) && (l == blas::Layout::ColMajor ? cols : rows) > 1;
+}
 template <typename sint_t>
 inline std::vector<int64_t> widen(const sint_t* p, int64_t n) { return std::vector<int64_t>(p, p + n); }
 
@@ -398,7 +403,8 @@ inline void sk3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, int6
         randblas_require(lda >= (layout == blas::Layout::ColMajor ? rA : cA));
         randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
         const uint64_t nA = span(layout, rA, cA, lda), nB = span(layout, rB, cB, ldb);
-        DevBuf dS(S.buff, (uint64_t) D.n_rows * D.n_cols * sizeof(T)), dA(A, nA * sizeof(T)), dB(beta != (T) 0 ? B : nullptr, nB * sizeof(T));
+        DevBuf dS(S.buff, (uint64_t) D.n_rows * D.n_cols * sizeof(T)), dA(A, nA * sizeof(T)),
+               dB((beta != (T) 0 || padded(layout, rB, cB, ldb)) ? B : nullptr, nB * sizeof(T));
         check(fn<T>::sketch_dense()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
                                     S.seed_state.counter, S.seed_state.key, (const T*) dS.p, ch(S.layout), ro_s, co_s, (const T*) dA.p, lda, beta,
                                     (T*) dB.p, ldb, nullptr), "sketch_general");
@@ -437,7 +443,8 @@ inline void sk3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, int6
     randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
     const uint64_t nA = span(layout, rA, cA, lda), nB = span(layout, rB, cB, ldb);
     const std::vector<int64_t> r64 = widen(S.rows, n), c64 = widen(S.cols, n);
-    DevBuf dr(r64.data(), n * 8), dc(c64.data(), n * 8), dv(S.vals, n * sizeof(T)), dA(A, nA * sizeof(T)), dB(beta != (T) 0 ? B : nullptr, nB * sizeof(T));
+    DevBuf dr(r64.data(), n * 8), dc(c64.data(), n * 8), dv(S.vals, n * sizeof(T)), dA(A, nA * sizeof(T)),
+           dB((beta != (T) 0 || padded(layout, rB, cB, ldb)) ? B : nullptr, nB * sizeof(T));
     check(fn<T>::spmm_coo()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, n, (const int64_t*) dr.p, (const int64_t*) dc.p,
                             (const T*) dv.p, ro_s, co_s, (const T*) dA.p, lda, beta, (T*) dB.p, ldb, nullptr), "sketch_general");
     check(rbx_memcpy_d2h(B, dB.p, nB * sizeof(T), nullptr), "rbx_memcpy_d2h");
@@ -630,7 +637,8 @@ inline void sksp3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, in
     randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
     const uint64_t nB = span(layout, rB, cB, ldb);
     const std::vector<int64_t> a0 = widen(i0, n0), a1 = widen(i1, n1);
-    DevBuf d0(a0.data(), n0 * 8), d1(a1.data(), n1 * 8), dv(A.vals, A.nnz * sizeof(T)), dB(beta != (T) 0 ? B : nullptr, nB * sizeof(T));
+    DevBuf d0(a0.data(), n0 * 8), d1(a1.data(), n1 * 8), dv(A.vals, A.nnz * sizeof(T)),
+           dB((beta != (T) 0 || padded(layout, rB, cB, ldb)) ? B : nullptr, nB * sizeof(T));
     check(fn<T>::sparsedata()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
                               S.seed_state.counter, S.seed_state.key, ro_s, co_s, fmt, A.n_rows, A.n_cols, A.nnz, (const T*) dv.p,
                               (const int64_t*) d0.p, (const int64_t*) d1.p, ro_a, co_a, beta, (T*) dB.p, ldb, nullptr), "sketch_sparse");

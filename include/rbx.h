@@ -28,6 +28,7 @@ extern "C" {
 #define RBX_ERR_NO_DEVICE  -3   /* no sm_100 device visible */
 #define RBX_ERR_ALLOC      -4   /* device workspace allocation failed */
 #define RBX_ERR_UNSUPPORTED -5  /* valid in the reference, not implemented on the device yet */
+#define RBX_ERR_COMM       -7   /* NCCL missing (libnccl.so.2 could not be loaded) or an NCCL call failed */
 #define RBX_ERR_TOO_LARGE  -6   /* beyond the fixed capacity of an allocation-free entry point (rbx_sketch_vector_noalloc) */
 
 const char* rbx_strerror(int code);
@@ -42,8 +43,9 @@ int rbx_free(void* dev_ptr);
 int rbx_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* stream);
 int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream);
 int rbx_stream_synchronize(void* stream);
-/* Kernel workspaces (operator codes, split partials, operator slabs) come from the device's default stream-ordered pool and
-   stay mapped between calls; this synchronises the device and returns them to the driver. */
+/* Kernel workspaces (operator codes, split partials, operator slabs) come from a private stream-ordered pool per device
+   (never the default pool the application shares) that keeps up to 1/32 of the device's memory mapped between calls
+   (RBX_WS_KEEP_MB overrides); this synchronises the device and returns all of it to the driver. */
 int rbx_trim_workspace(void);
 
 /* ---- RNG state algebra (host-side, exact) ------------------------------------------------------ */
@@ -216,8 +218,46 @@ int rbx_sketch_sparsedata_f64(char side, char layout, char opS, char opA, int64_
                               const double* vals_dev, const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t ro_a, int64_t co_a,
                               double beta, double* B_dev, int64_t ldb, void* stream);
 
-/* ---- sharding helper for the multi-GPU callers: rank's [start, start+len) of `total`, aligned ---- */
+/* ---- multi-GPU (reference contract: rtd/source/tutorial/updates.rst:59-80, skge.hh:182-189) ----------------------
+ * One process per GPU. rbx_shard_range: rank's [start, start+len) of `total`, in units of `align`.
+ * Column-sharded sketches need no entry point: every rank calls rbx_sketch_* on its own column slab with the same operator.
+ * Row-sharded left sketches: rbx_shard_sketch_*: rank r holds rows [start_r, start_r + len_r) of op(A)
+ * (rbx_shard_range(m_total, world, rank, align)); it sketches them with the operator's column offset co_s + start_r (beta is
+ * applied on rank 0 only, so beta * B enters the sum once), then ONE NCCL collective on `stream` sums the d x n partials:
+ * ncclReduceScatter into B_piece_dev (d * n / world elements: rank r receives elements [r, r+1) * d * n / world of the
+ * flattened B; d * n must divide by world) or, with B_piece_dev == NULL, ncclAllReduce in place. B must be dense
+ * (ldb == d for 'C', n for 'R'). comm == NULL or world == 1: no collective (B_piece_dev, if given, receives a copy).
+ * The communicator: rank 0 calls rbx_comm_unique_id and hands the 128 bytes to the other ranks by whatever channel the
+ * application has (MPI, torch.distributed, a file); every rank then calls rbx_comm_init with its device current.
+ * NCCL is loaded at run time (libnccl.so.2, or RBX_NCCL_LIBRARY); without it these calls return RBX_ERR_COMM. */
 void rbx_shard_range(int64_t total, int world, int rank, int64_t align, int64_t* start, int64_t* len);
+int rbx_comm_unique_id(uint8_t id[128]);
+int rbx_comm_init(void** comm, int world, int rank, const uint8_t id[128]);
+int rbx_comm_destroy(void* comm);
+int rbx_comm_info(void* comm, int* world, int* rank, int* nccl_version);
+int rbx_comm_reduce_scatter_f32(void* comm, float* B_dev, int64_t count, float* piece_dev, void* stream);
+int rbx_comm_reduce_scatter_f64(void* comm, double* B_dev, int64_t count, double* piece_dev, void* stream);
+int rbx_comm_all_reduce_f32(void* comm, float* B_dev, int64_t count, void* stream);
+int rbx_comm_all_reduce_f64(void* comm, double* B_dev, int64_t count, void* stream);
+/* dense operator (lskge3 per rank, skge.hh:173-215) */
+int rbx_shard_sketch_dense_f32(void* comm, char layout, char opA, int64_t d, int64_t n, int64_t m_total, float alpha,
+                               int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                               int64_t ro_s, int64_t co_s, const float* A_local_dev, int64_t lda, float beta,
+                               float* B_dev, int64_t ldb, float* B_piece_dev, int64_t align, void* stream);
+int rbx_shard_sketch_dense_f64(void* comm, char layout, char opA, int64_t d, int64_t n, int64_t m_total, double alpha,
+                               int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                               int64_t ro_s, int64_t co_s, const double* A_local_dev, int64_t lda, double beta,
+                               double* B_dev, int64_t ldb, double* B_piece_dev, int64_t align, void* stream);
+/* sparse operator (lskges per rank, skge.hh:485-510): the columns [start_r, start_r + len_r) of a wide SASO are exactly the
+ * Fisher-Yates vectors of those indices, so a rank regenerates only its own part of S */
+int rbx_shard_sketch_sparseop_f32(void* comm, char layout, char opA, int64_t d, int64_t n, int64_t m_total, float alpha,
+                                  int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                  int64_t ro_s, int64_t co_s, const float* A_local_dev, int64_t lda, float beta,
+                                  float* B_dev, int64_t ldb, float* B_piece_dev, int64_t align, void* stream);
+int rbx_shard_sketch_sparseop_f64(void* comm, char layout, char opA, int64_t d, int64_t n, int64_t m_total, double alpha,
+                                  int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                  int64_t ro_s, int64_t co_s, const double* A_local_dev, int64_t lda, double beta,
+                                  double* B_dev, int64_t ldb, double* B_piece_dev, int64_t align, void* stream);
 
 #ifdef __cplusplus
 }

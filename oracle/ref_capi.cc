@@ -53,6 +53,14 @@ int ref_blas_threads() {
     return be.get_threads ? be.get_threads() : omp_get_max_threads();
 }
 int ref_omp_threads() { return omp_get_max_threads(); }
+// bench.py: torch.distributed.run exports OMP_NUM_THREADS=1; the CPU legs ask for every host core explicitly
+int ref_set_threads(int n) {
+    if (n < 1) n = 1;
+    omp_set_num_threads(n);
+    auto& be = blas_shim::backend();
+    if (be.set_threads) be.set_threads(n);
+    return omp_get_max_threads();
+}
 
 // ---- raw generator pieces (Random123 shim + random_gen.hh) --------------------------
 int ref_philox4x32(const uint32_t* ctr, const uint32_t* key, uint32_t* out) {

@@ -14,7 +14,7 @@ LIBPATH = os.environ.get("RBX_LIBRARY") or os.path.join(_HERE, "librbx.so")
 
 _CT = {
     "void": None, "char": ctypes.c_char, "int": ctypes.c_int, "int64_t": ctypes.c_int64, "uint64_t": ctypes.c_uint64,
-    "float": ctypes.c_float, "double": ctypes.c_double,
+    "float": ctypes.c_float, "double": ctypes.c_double, "uint8_t": ctypes.c_uint8,
 }
 
 

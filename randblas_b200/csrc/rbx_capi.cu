@@ -259,13 +259,43 @@ static inline size_t span_elems(char layout, int64_t rows, int64_t cols, int64_t
     return (layout == 'C') ? (size_t)((cols - 1) * ld + rows) : (size_t)((rows - 1) * ld + cols);
 }
 
+// How the staged copy of B returns to the host when B is a window of a larger array (ldb beyond the natural dimension):
+// the kernels write only the rows x cols view, and the reference never touches the padding. Long unit-stride runs come back
+// with a strided copy of the view only; short runs (sketch_vector with incy > 1 is the extreme: one element per run) upload
+// the old contents first, so that the whole span can be copied back unchanged outside the view.
+struct HostView {
+    size_t span, inner, outer, ld;     // elements
+    bool strided_back;                 // copy back the view with cudaMemcpy2D (otherwise the whole span)
+    bool need_upload;                  // the padding of the device copy must hold the host's contents
+};
+template <typename T>
+static inline HostView host_view(char layout, int64_t rows, int64_t cols, int64_t ld) {
+    HostView v{};
+    v.span = span_elems(layout, rows, cols, ld);
+    v.inner = (size_t)(layout == 'C' ? rows : cols); v.outer = (size_t)(layout == 'C' ? cols : rows); v.ld = (size_t) ld;
+    const bool padded = v.span != 0 && v.outer > 1 && v.ld > v.inner;
+    v.strided_back = padded && v.inner * sizeof(T) >= 256;
+    v.need_upload = padded && !v.strided_back;
+    return v;
+}
+template <typename T>
+static inline cudaError_t copy_back_view(T* host, const T* dev, const HostView& v, cudaStream_t st) {
+    if (v.span == 0) return cudaSuccess;
+    if (v.strided_back)
+        return cudaMemcpy2DAsync(host, v.ld * sizeof(T), dev, v.ld * sizeof(T), v.inner * sizeof(T), v.outer, cudaMemcpyDeviceToHost, st);
+    return cudaMemcpyAsync(host, dev, v.span * sizeof(T), cudaMemcpyDeviceToHost, st);
+}
+
 // Stage host A / B through device memory around `body(A_dev, B_dev, stream)`.
 template <typename T, typename F>
 static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_host, int64_t lda,
                        int64_t rows_B, int64_t cols_B, T* B_host, int64_t ldb, bool read_B, F body) {
     { DryRun dry; RBX_TRY(body((const T*) nullptr, (T*) nullptr, nullptr)); }
     RBX_NEED_DEVICE();
-    const size_t nA = span_elems(layout, rows_A, cols_A, lda), nB = span_elems(layout, rows_B, cols_B, ldb);
+    const size_t nA = span_elems(layout, rows_A, cols_A, lda);
+    const HostView vb = host_view<T>(layout, rows_B, cols_B, ldb);
+    const size_t nB = vb.span;
+    read_B = read_B || vb.need_upload;
     T *A_dev = nullptr, *B_dev = nullptr;
     cudaStream_t st = nullptr;
     int rc = RBX_OK;
@@ -275,7 +305,7 @@ static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_h
     if (rc == RBX_OK && nA && cudaMemcpyAsync(A_dev, A_host, nA * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
     if (rc == RBX_OK && nB && read_B && cudaMemcpyAsync(B_dev, B_host, nB * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
     if (rc == RBX_OK) rc = body(A_dev, B_dev, (void*) st);
-    if (rc == RBX_OK && nB && cudaMemcpyAsync(B_host, B_dev, nB * sizeof(T), cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK && copy_back_view<T>(B_host, B_dev, vb, st) != cudaSuccess) rc = RBX_ERR_CUDA;
     if (cudaStreamSynchronize(st) != cudaSuccess && rc == RBX_OK) rc = RBX_ERR_CUDA;
     cudaFree(A_dev); cudaFree(B_dev);
     return rc;
@@ -288,7 +318,8 @@ template <typename T, typename F>
 static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, const T* A_host, int64_t lda, T beta,
                              T* B_host, int64_t ldb, F body) {
     RBX_NEED_DEVICE();
-    const size_t nB = span_elems(layout, rows_B, N, ldb);
+    const HostView vb = host_view<T>(layout, rows_B, N, ldb);
+    const size_t nB = vb.span;
     int64_t klen = (int64_t)((size_t) 512 << 20) / (N * (int64_t) sizeof(T));
     klen = (klen / 512) * 512;
     if (klen < 512) klen = 512;
@@ -305,7 +336,7 @@ static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, 
         ok(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking)); ok(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
         for (int b = 0; b < 2; ++b) { ok(cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming)); ok(cudaEventCreateWithFlags(&consumed[b], cudaEventDisableTiming)); }
     }
-    if (rc == RBX_OK && beta != (T) 0) ok(cudaMemcpyAsync(B_dev, B_host, nB * sizeof(T), cudaMemcpyHostToDevice, sx));
+    if (rc == RBX_OK && (beta != (T) 0 || vb.need_upload)) ok(cudaMemcpyAsync(B_dev, B_host, nB * sizeof(T), cudaMemcpyHostToDevice, sx));
     for (int64_t i = 0; i < nslab && rc == RBX_OK; ++i) {
         const int b = (int)(i & 1);
         const int64_t k0 = i * klen, kl = (k0 + klen < K) ? klen : K - k0;
@@ -325,7 +356,7 @@ static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, 
         if (rc == RBX_OK) rc = body(k0, kl, (const T*) slab[b], lda_slab, i == 0 ? beta : (T) 1, B_dev, (void*) sx);
         ok(cudaEventRecord(consumed[b], sx));
     }
-    if (rc == RBX_OK) ok(cudaMemcpyAsync(B_host, B_dev, nB * sizeof(T), cudaMemcpyDeviceToHost, sx));
+    if (rc == RBX_OK) ok(copy_back_view<T>(B_host, B_dev, vb, sx));
     if (sx) ok(cudaStreamSynchronize(sx));
     if (sc) ok(cudaStreamSynchronize(sc));
     for (int b = 0; b < 2; ++b) { if (copied[b]) cudaEventDestroy(copied[b]); if (consumed[b]) cudaEventDestroy(consumed[b]); }
@@ -463,7 +494,7 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
     }
     // the operator window is generated in slabs of the contraction axis, as floats, Mp x Ks at a time (i contiguous)
     const int64_t Mp = (s.M + 3) & ~(int64_t) 3;
-    const int64_t budget = (int64_t) 4 << 30;
+    const int64_t budget = (int64_t) ws_budget((size_t) 4 << 30);       // at most 4 GiB, at most a quarter of the free memory
     int64_t Ks = budget / (4 * Mp);
     if (const char* ev = getenv("RBX_SPD_SLAB")) { const int64_t v = atoll(ev); if (v >= 1) Ks = v; }
     if (Ks < 1) Ks = 1;
@@ -535,6 +566,7 @@ const char* rbx_strerror(int code) {
         case RBX_ERR_NO_DEVICE: return "no sm_100 CUDA device visible (there is no CPU fallback)";
         case RBX_ERR_ALLOC: return "device workspace allocation failed";
         case RBX_ERR_UNSUPPORTED: return "case not implemented on the device";
+        case RBX_ERR_COMM: return "NCCL unavailable (libnccl.so.2 not loadable) or an NCCL call failed";
         case RBX_ERR_TOO_LARGE: return "problem exceeds the fixed scratch capacity of an allocation-free entry point";
         default: return "unknown rbx error code";
     }
@@ -751,8 +783,9 @@ int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* st
 int rbx_stream_synchronize(void* stream) { return cudaStreamSynchronize((cudaStream_t) stream) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA; }
 int rbx_trim_workspace(void) {
     int dev = 0;
-    cudaMemPool_t pool;
-    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetDefaultMemPool(&pool, dev) != cudaSuccess) return RBX_ERR_CUDA;
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetDevice(&dev) != cudaSuccess) return RBX_ERR_CUDA;
+    cudaMemPool_t pool = ws_pool(dev);
+    if (!pool) return RBX_OK;
     return cudaMemPoolTrimTo(pool, 0) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;
 }
 

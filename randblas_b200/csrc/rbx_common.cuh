@@ -2,6 +2,8 @@
 #pragma once
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <mutex>
 #include <cuda_runtime.h>
 #include "../../include/rbx.h"
 #include "rbx_rng.cuh"
@@ -18,34 +20,70 @@ inline int check_launch(const char* what) {
     }
     return RBX_OK;
 }
-// Stream-ordered workspace from the device's default memory pool. The pool's release threshold is raised once per device
-// so that a workspace freed by one call is still mapped for the next (the default threshold of 0 hands the memory back to
-// the driver at every synchronisation: re-mapping a few hundred MB costs more than the kernels here).
-// rbx_trim_workspace() gives it back.
+// Stream-ordered workspaces come from a PRIVATE memory pool per device (cudaMemPoolCreate), not from the device's default
+// pool that the host application and other libraries (torch's allocator, cuBLAS) share: nothing this library does changes
+// their pool's behaviour. The private pool keeps up to a bounded amount mapped between calls (release threshold = 1/32 of
+// the device's memory, 5.6 GiB on a B200; RBX_WS_KEEP_MB overrides) -- a workspace freed by one call is still mapped for the
+// next, because re-mapping a few hundred MB costs more than the kernels here -- and hands anything above that back to the
+// driver at the next synchronisation. rbx_trim_workspace() returns all of it. Creation is guarded by std::call_once.
+struct WsState {
+    cudaMemPool_t pool[64] = {};
+    cudaStream_t aux[64] = {};
+    std::once_flag pool_once[64], aux_once[64];
+};
+inline WsState& ws_state() { static WsState s; return s; }
+inline cudaMemPool_t ws_pool(int dev) {
+    WsState& S = ws_state();
+    if (dev < 0 || dev >= 64) return nullptr;
+    std::call_once(S.pool_once[dev], [&S, dev] {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) { cudaGetLastError(); return; }
+        size_t free_b = 0, total_b = 0;
+        unsigned long long keep = 4ull << 30;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) keep = (unsigned long long) total_b / 32; else cudaGetLastError();
+        if (const char* ev = getenv("RBX_WS_KEEP_MB")) keep = (unsigned long long) atoll(ev) << 20;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        S.pool[dev] = pool;
+    });
+    return S.pool[dev];
+}
 inline cudaError_t ws_alloc(void** p, size_t bytes, cudaStream_t stream) {
-    static bool raised[64] = {};
     int dev = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && !raised[dev]) {
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-            unsigned long long keep = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-        }
-        raised[dev] = true;
-    }
-    return cudaMallocAsync(p, bytes, stream);
+    if (cudaGetDevice(&dev) != cudaSuccess) return cudaGetLastError();
+    cudaMemPool_t pool = ws_pool(dev);
+    return pool ? cudaMallocFromPoolAsync(p, bytes, pool, stream) : cudaMallocAsync(p, bytes, stream);
 }
 template <typename P> inline cudaError_t ws_alloc(P** p, size_t bytes, cudaStream_t stream) {
     return ws_alloc(reinterpret_cast<void**>(p), bytes, stream);
 }
+// bytes a single workspace may take: a quarter of what is free now (the sketch_sparse operator slab sizes itself with this)
+inline size_t ws_budget(size_t want) {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return want; }
+    int dev = 0; cudaGetDevice(&dev);
+    unsigned long long cached = 0, used = 0;                   // memory the private pool holds but no call is using counts as free
+    if (cudaMemPool_t pool = ws_pool(dev)) {
+        if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &cached) != cudaSuccess) { cudaGetLastError(); cached = 0; }
+        if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) != cudaSuccess) { cudaGetLastError(); used = 0; }
+    }
+    const size_t avail = (free_b + (size_t)(cached > used ? cached - used : 0)) / 4;
+    return want < avail ? want : avail;
+}
 
 // one auxiliary (non-blocking) stream per device: operator panels are generated on it while the previous panel's GEMM runs
 inline cudaStream_t aux_stream() {
-    static cudaStream_t aux[64] = {};
+    WsState& S = ws_state();
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    if (!aux[dev] && cudaStreamCreateWithFlags(&aux[dev], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-    return aux[dev];
+    std::call_once(S.aux_once[dev], [&S, dev] {
+        if (cudaStreamCreateWithFlags(&S.aux[dev], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); S.aux[dev] = nullptr; }
+    });
+    return S.aux[dev];
 }
 
 #define RBX_CUDA_TRY(expr)                                                                   \

@@ -543,6 +543,42 @@ def test_host_pointer_entry_points(rb, cuda):
     assert np.array_equal(buf.numpy().view(np.uint32), exp.view(np.uint32))
 
 
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_host_pointer_padded_B_is_untouched_outside_the_view(rb, cuda, dt):
+    """B as a window of a larger host array (ldb beyond the natural dimension, incy > 1) with beta == 0: the reference never
+    touches the elements outside the rows x cols view, so they must come back bit-identical (the staged copy used
+    to return uninitialised device memory there). Long and short unit-stride runs take different copy-back strategies."""
+    rng = np.random.default_rng(77)
+    npdt = np.float32 if dt == "f32" else np.float64
+    for (layout, d, n, m, pad, sparse) in [("C", 100, 7, 300, 5, False), ("C", 8, 9, 200, 3, False), ("R", 6, 120, 200, 11, False),
+                                           ("R", 40, 5, 300, 2, True), ("C", 128, 6, 400, 64, True)]:
+        ldb = (d if layout == "C" else n) + pad
+        lda = m if layout == "C" else n
+        A = torch.from_numpy(rng.standard_normal(m * n).astype(npdt))
+        B0 = rng.standard_normal(span(layout, d, n, ldb)).astype(npdt)
+        B0[::3] = np.nan                                       # NaN in B with beta == 0 must not propagate either (util.hh:51-59)
+        Bh = torch.from_numpy(B0.copy())
+        S = rb.SparseSkOp(rb.SparseDist(d, m, 4), 3) if sparse else rb.DenseSkOp(rb.DenseDist(d, m), 3, dtype=TDT[dt])
+        rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A, lda, 0.0, Bh, ldb)
+        Bd = torch.from_numpy(B0.copy()).to(cuda)
+        rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A.to(cuda), lda, 0.0, Bd, ldb)
+        got, dev = Bh.numpy(), Bd.cpu().numpy()
+        mask = np.ones(len(B0), bool)
+        mask[mat(layout, d, n, ldb, np.arange(len(B0))).ravel()] = False
+        bits = np.uint32 if dt == "f32" else np.uint64
+        assert np.array_equal(got[mask].view(bits), B0[mask].view(bits)), (layout, d, n, pad)
+        assert np.isfinite(got[~mask]).all()
+        assert np.allclose(got[~mask], dev[~mask], rtol=1e-5 if dt == "f32" else 1e-12, atol=1e-5 if dt == "f32" else 1e-12)
+    # sketch_vector with a strided y on the host
+    d, m, incy = 300, 5000, 3
+    x = torch.from_numpy(rng.standard_normal(m).astype(npdt))
+    y0 = rng.standard_normal(d * incy).astype(npdt)
+    y = torch.from_numpy(y0.copy())
+    rb.sketch_vector(rb.Op.NoTrans, d, m, 1.0, rb.DenseSkOp(rb.DenseDist(d, m), 5, dtype=TDT[dt]), 0, 0, x, 1, 0.0, y, incy)
+    gap = np.ones(len(y0), bool); gap[::incy] = False
+    assert np.array_equal(y.numpy()[gap], y0[gap]) and not np.array_equal(y.numpy()[::incy], y0[::incy])
+
+
 @pytest.mark.parametrize("layout", ["C", "R"])
 def test_host_pointer_pipelined_slabs(rb, cuda, layout):
     """host matrices of >= 1 GiB are sketched slab by slab (copy of slab i+1 overlaps the sketch of slab i, co_s advanced per
