@@ -1,0 +1,1 @@
+#include "../RandBLAS_b200.hh"   // forwards to the single B200 header (reference: RandBLAS/skge.hh)

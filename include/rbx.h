@@ -204,6 +204,17 @@ int rbx_sparse_regroup_f64(char by, char fmt_in, int64_t n_rows, int64_t n_cols,
                            const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t* ptr_out_dev, int64_t* idx_out_dev,
                            double* vals_out_dev, void* stream);
 
+/* util::require_symmetric (util.hh:165-188) for a device-resident n x n matrix: RBX_ERR_ARG when some pair violates
+ * |A_ij - A_ji| <= (|A_ij| + |A_ji| + 1) * tol (the reference throws "Symmetry check failed"); tol < 0 skips the check.
+ * One kernel over the upper triangle and a 4-byte read-back; synchronises the stream. (sksy.hh:165-184 calls it before sketching) */
+int rbx_require_symmetric_f32(char layout, const float* A_dev, int64_t n, int64_t lda, float tol, void* stream);
+int rbx_require_symmetric_f64(char layout, const double* A_dev, int64_t n, int64_t lda, double tol, void* stream);
+
+/* outer index of every nonzero of a CSR (rows) / CSC (columns) matrix from its pointer array: the device-side step of viewing
+ * compressed data as COO triplets (left_spmm / right_spmm on CSR / CSC, spmm_dispatch.hh:48-200). outer_idx_dev has nnz =
+ * ptr[n_outer] entries. */
+int rbx_expand_ptr(int64_t n_outer, const int64_t* ptr_dev, int64_t* outer_idx_dev, void* stream);
+
 /* ---- sketch_sparse: dense operator x sparse data, sparse_data::lsksp3 / rsksp3, sksp.hh:147-192 / 302-345 */
 /* fmt 'O' COO (idx0 = rows, idx1 = cols), 'R' CSR (idx0 = rowptr, idx1 = colidxs), 'C' CSC (idx0 = rowidxs,
  * idx1 = colptr); int64 indices, index_base Zero. CSR/CSC require ro_a == co_a == 0 (spmm_dispatch.hh:99-104). */

@@ -422,8 +422,15 @@ def sketch_vector(opS, *rest):
 
 
 def require_symmetric(layout, A, n, lda, tol):
-    """util::require_symmetric (util.hh:165-188). A precondition check, not part of the timed path."""
+    """util::require_symmetric (util.hh:165-188): a precondition check, not part of the timed path. Device tensors are
+    checked by one kernel over the upper triangle (rbx_require_symmetric_*); host tensors on the host, like the reference."""
     if tol < 0:
+        return
+    if A.is_cuda:
+        rc = getattr(lib, f"rbx_require_symmetric_{_suf(A.dtype)}")(_c(layout), _ptr(A), n, lda, _scalar(A.dtype, tol), _stream(A))
+        if rc == -1:
+            raise Error("Symmetry check failed.")
+        check(rc, "rbx_require_symmetric")
         return
     M = torch.as_strided(A, (n, n), (1, lda) if Layout(layout) == Layout.ColMajor else (lda, 1))
     viol = (M - M.T).abs()

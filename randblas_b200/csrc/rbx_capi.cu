@@ -388,10 +388,9 @@ static int spmm_coo(char side, char layout, char opS, char opA, int64_t p0, int6
     RBX_REQUIRE(S_rows >= s.rows_sub && S_cols >= s.cols_sub);               // spmm_dispatch.hh:94-96 (COO: >=)
     RBX_NEED_DEVICE();
     cudaStream_t st = (cudaStream_t) stream;
-    RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));    // spmm_dispatch.hh:122-132
-    if (alpha == (T) 0) return RBX_OK;                                       // spmm_dispatch.hh:134-135
-    return launch_coo_scatter<T, I>(nnz, rows, cols, vals, s.s_trans, ro_s, co_s, s.M, s.N, s.K, alpha,
-                                    A, s.sx_l, s.sx_j, B, s.sc_i, s.sc_j, st);
+    // beta scaling (spmm_dispatch.hh:122-132) and the alpha == 0 early exit (:134-135) are part of the gather's single store
+    return launch_coo_gather<T>(nnz, rows, cols, vals, s.s_trans, ro_s, co_s, s.M, s.N, s.K, alpha,
+                                A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
 }
 
 template <typename T>
@@ -423,8 +422,9 @@ static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p
                                            A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
         if (rc != RBX_ERR_UNSUPPORTED) return rc;
     }
-    RBX_TRY(launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st));
-    if (alpha == (T) 0) return RBX_OK;
+    if (alpha == (T) 0) return launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st);
+    // general path: regenerate the triplets (fill_sparse), then the deterministic output-stationary product; nothing is
+    // written to B before every workspace has been allocated
     const size_t nnz = (size_t)(vec_nnz * (major_axis == 'S' ? lng : sht));
     int64_t *rows = nullptr, *cols = nullptr; T* vals = nullptr;
     if (ws_alloc(&rows, nnz * 8, st) != cudaSuccess || ws_alloc(&cols, nnz * 8, st) != cudaSuccess ||
@@ -436,8 +436,8 @@ static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p
     }
     int rc = fill_sparse<T, int64_t>(S_rows, S_cols, vec_nnz, major_axis, ctr, key, rows, cols, vals, nullptr, stream);
     if (rc == RBX_OK)
-        rc = launch_coo_scatter<T, int64_t>((int64_t) nnz, rows, cols, vals, s.s_trans, ro_s, co_s, s.M, s.N, s.K, alpha,
-                                            A, s.sx_l, s.sx_j, B, s.sc_i, s.sc_j, st);
+        rc = launch_coo_gather<T>((int64_t) nnz, rows, cols, vals, s.s_trans, ro_s, co_s, s.M, s.N, s.K, alpha,
+                                  A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
     cudaFreeAsync(rows, st); cudaFreeAsync(cols, st); cudaFreeAsync(vals, st);
     return rc;
 }
@@ -705,6 +705,32 @@ RBX_DEF_SPARSE(f32_i64, float, int64_t)
 RBX_DEF_SPARSE(f64_i32, double, int32_t)
 RBX_DEF_SPARSE(f64_i64, double, int64_t)
 
+#define RBX_DEF_SYM(SUF, T)                                                                                                       \
+int rbx_require_symmetric_##SUF(char layout, const T* A_dev, int64_t n, int64_t lda, T tol, void* stream) {                       \
+    RBX_REQUIRE(is_layout(layout) && n >= 0 && lda >= n);                                                                         \
+    if (tol < (T) 0 || n <= 1) return RBX_OK;                                   /* util.hh:166: a negative tolerance skips the check */ \
+    RBX_NEED_DEVICE();                                                                                                            \
+    cudaStream_t st = (cudaStream_t) stream;                                                                                      \
+    int* flag = nullptr;                                                                                                          \
+    if (ws_alloc(&flag, sizeof(int), st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }                            \
+    int rc = cudaMemsetAsync(flag, 0, sizeof(int), st) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;                                    \
+    int64_t s_row, s_col; strides_of(layout, lda, &s_row, &s_col);                                                                \
+    if (rc == RBX_OK) rc = launch_require_symmetric<T>(A_dev, n, s_row, s_col, tol, flag, st);                                    \
+    int host_flag = 0;                                                                                                            \
+    if (rc == RBX_OK && (cudaMemcpyAsync(&host_flag, flag, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess ||             \
+                         cudaStreamSynchronize(st) != cudaSuccess)) rc = RBX_ERR_CUDA;                                            \
+    cudaFreeAsync(flag, st);                                                                                                      \
+    if (rc != RBX_OK) return rc;                                                                                                  \
+    return host_flag ? RBX_ERR_ARG : RBX_OK;                                                                                      \
+}
+RBX_DEF_SYM(f32, float)
+RBX_DEF_SYM(f64, double)
+
+int rbx_expand_ptr(int64_t n_outer, const int64_t* ptr_dev, int64_t* outer_idx_dev, void* stream) {
+    RBX_REQUIRE(n_outer >= 0);
+    RBX_NEED_DEVICE();
+    return launch_expand_ptr(n_outer, ptr_dev, outer_idx_dev, (cudaStream_t) stream);
+}
 int rbx_sparse_regroup_f32(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const float* vals_dev,
                            const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t* ptr_out_dev, int64_t* idx_out_dev,
                            float* vals_out_dev, void* stream) {

@@ -52,18 +52,9 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
 // C = beta * C over an M x N strided view (beta == 0 writes zeros without reading: util.hh:51-59)
 template <typename T> int launch_scale_view(T* C, int64_t M, int64_t N, int64_t sc_i, int64_t sc_j, T beta, cudaStream_t stream);
 
-// C[i, :] += alpha * v * X[l, :] for every COO entry (r, c, v) whose op'd coordinates fall in the window:
-// (i, l) = trans ? (c - co, r - ro) : (r - ro, c - co), 0 <= i < M, 0 <= l < K.
-template <typename T, typename I>
-int launch_coo_scatter(int64_t nnz, const I* rows, const I* cols, const T* vals, bool trans, int64_t ro, int64_t co,
-                       int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
-                       T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
-
-// C[:, j] += alpha * v * Sd[:, l] for every sparse-data entry (p, q, v): (l, j) = trans ? (q - co, p - ro) : (p - ro, q - co);
-// Sd is the M x K operator window stored with i contiguous (Sd[i + l * M]).
+// util::require_symmetric on the device (util.hh:165-188): raises *violated_dev when some |A_ij - A_ji| exceeds its tolerance
 template <typename T>
-int launch_spdata_scatter(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
-                          int64_t M, int64_t N, int64_t K, T alpha, const T* Sd, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+int launch_require_symmetric(const T* A, int64_t n, int64_t s_row, int64_t s_col, T tol, int* violated_dev, cudaStream_t stream);
 
 // K5 (rbx_spdata.cu): output-stationary gather. Column j of C gets alpha * sum over the entries (l, v) of segment j of
 // v * Sd[(l - l0) * Mp + i]; `first` applies beta (C not read when beta == 0), later slabs accumulate.
@@ -74,7 +65,16 @@ int launch_spdata_gather(int64_t N, const int64_t* ptr, const int64_t* lidx, con
 // stream-ordered allocations the caller releases with cudaFreeAsync.
 template <typename T>
 int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
-                        int64_t K, int64_t N, int64_t** ptr_out, int64_t** lidx_out, T** vals_out, cudaStream_t stream);
+                        int64_t K, int64_t N, int64_t** ptr_out, int64_t** lidx_out, T** vals_out, cudaStream_t stream,
+                        int lc_shift = 62, int64_t nlc = 1);   // nlc > 1: sub-segments per block of 2^lc_shift contraction indices
+
+// Deterministic general sparse-operator product (rbx_spmm_gather.cu): C = alpha * Sop * X + beta * C for COO triplets,
+// (i, l) = trans ? (c - co, r - ro) : (r - ro, c - co); entries are regrouped by output row on the device and every output
+// element is summed by one warp in a fixed order -- no atomics. beta is applied here (C is not read when beta == 0).
+template <typename T>
+int launch_coo_gather(int64_t nnz, const int64_t* rows, const int64_t* cols, const T* vals, bool trans, int64_t ro, int64_t co,
+                      int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
+                      T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
 
 // expand a CSR rowptr / CSC colptr (n_outer + 1 entries) into one outer index per nonzero
 int launch_expand_ptr(int64_t n_outer, const int64_t* ptr, int64_t* outer_idx, cudaStream_t stream);

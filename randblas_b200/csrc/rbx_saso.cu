@@ -45,6 +45,7 @@ constexpr int SASO_WARPS = 16;
 constexpr int SASO_RW = 64;         // rows of B per warp
 constexpr int SASO_R = SASO_WARPS * SASO_RW;   // rows of B per CTA
 constexpr int SASO_THREADS = SASO_WARPS * 32;
+constexpr int SASO_MAX_RB = 8;      // row blocks of 1024 rows: operator windows of up to 8192 rows take the streaming kernel
 // ring stages: row-contiguous data runs two long chunks (compute per chunk far exceeds the copy latency, and a longer
 // chunk means more entries per accumulator slot); the slower element-wise copy of column-contiguous data wants three
 #ifndef SASO_NST_COLS_VAL
@@ -200,9 +201,9 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
     __syncthreads();
     block_excl_scan(tailcnt, slotoff, nslots, wtot);
     // first tail element of each row block, and whether any bucket of the chunk spills out of its region
-    uint32_t rb_base[4];
+    uint32_t rb_base[SASO_MAX_RB];
     bool any_spill = false;
-    for (int rb = 0; rb < 4; ++rb) {
+    for (int rb = 0; rb < SASO_MAX_RB; ++rb) {
         const int q0 = rb * SASO_WARPS * NS, q1 = (rb + 1) * SASO_WARPS * NS;
         rb_base[rb] = slotoff[q0 < nslots ? q0 : nslots];
         any_spill = any_spill || (slotoff[q1 < nslots ? q1 : nslots] - rb_base[rb] > (uint32_t) cap);
@@ -615,7 +616,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     // envelope of this kernel; everything else goes to the general path
     const bool cols_contig = (sx_l == 1 && sx_j != 1);
     if (!cols_contig && sx_j != 1) return RBX_ERR_UNSUPPORTED;
-    if (vec_nnz > 32 || M > 4 * SASO_R || M < 1 || N < 1 || K < 64) return RBX_ERR_UNSUPPORTED;
+    if (vec_nnz > 32 || M > SASO_MAX_RB * SASO_R || M < 1 || N < 1 || K < 64) return RBX_ERR_UNSUPPORTED;
     const int64_t ld = cols_contig ? sx_j : sx_l;
     if (reinterpret_cast<uintptr_t>(X) % 16 != 0 || (ld * (int64_t) sizeof(T)) % 16 != 0) return RBX_ERR_UNSUPPORTED;
     if (K > (int64_t) 0x7fffffff - 512 || N > 0x7fffffff) return RBX_ERR_UNSUPPORTED;

@@ -26,12 +26,16 @@ __device__ __forceinline__ bool map_entry(int64_t p, int64_t q, bool trans, int6
     return *l >= 0 && *l < K && *j >= 0 && *j < N;
 }
 
+// Segments are keyed by j * nlc + (l >> lc_shift): nlc == 1 groups by column j alone (sketch_sparse, conversions); nlc > 1
+// cuts every column into sub-segments by blocks of 2^lc_shift contraction indices, which keeps the segments that the rank
+// sort sees short however many entries a column has (the general sparse-operator path, rbx_spmm_gather.cu). Sub-segments
+// of one column are adjacent and in increasing l-block order, so a column's entries still come out sorted by l.
 __global__ void __launch_bounds__(256) spd_count_kernel(int64_t nnz, const int64_t* __restrict__ prow, const int64_t* __restrict__ pcol,
-                                                       bool trans, int64_t ro, int64_t co, int64_t K, int64_t N,
+                                                       bool trans, int64_t ro, int64_t co, int64_t K, int64_t N, int lc_shift, int64_t nlc,
                                                        unsigned long long* __restrict__ cnt) {
     for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t) gridDim.x * blockDim.x) {
         int64_t l, j;
-        if (map_entry(prow[e], pcol[e], trans, ro, co, K, N, &l, &j)) atomicAdd(cnt + j, 1ull);
+        if (map_entry(prow[e], pcol[e], trans, ro, co, K, N, &l, &j)) atomicAdd(cnt + (j * nlc + (l >> lc_shift)), 1ull);
     }
 }
 
@@ -84,11 +88,12 @@ template <typename T> struct __align__(16) SpdRec { int64_t l; T v; };
 template <typename T>
 __global__ void __launch_bounds__(256) spd_scatter_kernel(int64_t nnz, const int64_t* __restrict__ prow, const int64_t* __restrict__ pcol,
                                                          const T* __restrict__ vals, bool trans, int64_t ro, int64_t co, int64_t K, int64_t N,
+                                                         int lc_shift, int64_t nlc,
                                                          unsigned long long* __restrict__ cursor, SpdRec<T>* __restrict__ out) {
     for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += (int64_t) gridDim.x * blockDim.x) {
         int64_t l, j;
         if (map_entry(prow[e], pcol[e], trans, ro, co, K, N, &l, &j)) {
-            const unsigned long long pos = atomicAdd(cursor + j, 1ull);
+            const unsigned long long pos = atomicAdd(cursor + (j * nlc + (l >> lc_shift)), 1ull);
             SpdRec<T> r; r.l = l; r.v = vals[e];
             out[pos] = r;
         }
@@ -248,8 +253,12 @@ int launch_spdata_gather(int64_t N, const int64_t* ptr, const int64_t* lidx, con
 
 template <typename T>
 int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
-                        int64_t K, int64_t N, int64_t** ptr_out, int64_t** lidx_out, T** vals_out, cudaStream_t stream) {
+                        int64_t K, int64_t N_cols, int64_t** ptr_out, int64_t** lidx_out, T** vals_out, cudaStream_t stream,
+                        int lc_shift, int64_t nlc) {
     *ptr_out = nullptr; *lidx_out = nullptr; *vals_out = nullptr;
+    if (nlc < 1) { nlc = 1; lc_shift = 62; }
+    if (nlc == 1) lc_shift = 62;                       // l >> 62 == 0 for every valid l
+    const int64_t N = N_cols * nlc;                    // number of segments
     const int64_t nb = (N + 1 + 1023) / 1024;
     unsigned long long *cnt = nullptr, *cursor = nullptr, *bsum = nullptr;
     int64_t *ptr = nullptr, *out_l = nullptr; T* out_v = nullptr; SpdRec<T>* tmp = nullptr;
@@ -265,11 +274,11 @@ int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, c
         int64_t blocks = (nnz + 255) / 256;
         if (blocks > kNumSMs * 32) blocks = kNumSMs * 32;
         if (blocks < 1) blocks = 1;
-        spd_count_kernel<<<(unsigned) blocks, 256, 0, stream>>>(nnz, prow, pcol, trans, ro, co, K, N, cnt);
+        spd_count_kernel<<<(unsigned) blocks, 256, 0, stream>>>(nnz, prow, pcol, trans, ro, co, K, N_cols, lc_shift, nlc, cnt);
         spd_scan_partial_kernel<<<(unsigned) nb, 256, 0, stream>>>(N, cnt, bsum);
         spd_scan_blocks_kernel<<<1, 1, 0, stream>>>(nb, bsum);
         spd_scan_final_kernel<<<(unsigned) nb, 256, 0, stream>>>(N, cnt, bsum, ptr, cursor);
-        spd_scatter_kernel<T><<<(unsigned) blocks, 256, 0, stream>>>(nnz, prow, pcol, vals, trans, ro, co, K, N, cursor, tmp);
+        spd_scatter_kernel<T><<<(unsigned) blocks, 256, 0, stream>>>(nnz, prow, pcol, vals, trans, ro, co, K, N_cols, lc_shift, nlc, cursor, tmp);
         int64_t sb = (N * 32 + 255) / 256;
         if (sb > kNumSMs * 32) sb = kNumSMs * 32;
         if (sb < 1) sb = 1;
@@ -295,7 +304,7 @@ int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, c
     template int launch_spdata_gather<T>(int64_t, const int64_t*, const int64_t*, const T*, int64_t, int64_t, int64_t, int64_t,   \
                                          const float*, bool, bool, T, T, T*, int64_t, int64_t, cudaStream_t);                    \
     template int spd_group_by_column<T>(int64_t, const int64_t*, const int64_t*, const T*, bool, int64_t, int64_t, int64_t,       \
-                                        int64_t, int64_t**, int64_t**, T**, cudaStream_t);
+                                        int64_t, int64_t**, int64_t**, T**, cudaStream_t, int, int64_t);
 RBX_INST_SPD(float) RBX_INST_SPD(double)
 #undef RBX_INST_SPD
 

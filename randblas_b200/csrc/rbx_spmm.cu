@@ -35,106 +35,6 @@ int launch_scale_view(T* C, int64_t M, int64_t N, int64_t sc_i, int64_t sc_j, T 
 template int launch_scale_view<float>(float*, int64_t, int64_t, int64_t, int64_t, float, cudaStream_t);
 template int launch_scale_view<double>(double*, int64_t, int64_t, int64_t, int64_t, double, cudaStream_t);
 
-// One warp per entry, lanes along the columns of X / C (use when rows of X are contiguous).
-template <typename T, typename I>
-__global__ void __launch_bounds__(256) coo_scatter_rows_kernel(int64_t nnz, const I* __restrict__ rows, const I* __restrict__ cols,
-                                                              const T* __restrict__ vals, bool trans, int64_t ro, int64_t co,
-                                                              int64_t M, int64_t N, int64_t K, T alpha, const T* __restrict__ X,
-                                                              int64_t sx_l, int64_t sx_j, T* __restrict__ C, int64_t sc_i, int64_t sc_j) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
-    for (int64_t e = warp; e < nnz; e += nwarps) {
-        const int64_t r = (int64_t) rows[e] - ro, c = (int64_t) cols[e] - co;
-        const int64_t i = trans ? c : r, l = trans ? r : c;
-        if (i < 0 || i >= M || l < 0 || l >= K) continue;
-        const T v = alpha * vals[e];
-        const T* x = X + l * sx_l;
-        T* out = C + i * sc_i;
-        for (int64_t j = lane; j < N; j += 32) atomicAdd(out + j * sc_j, v * x[j * sx_j]);
-    }
-}
-
-// One thread per entry, walking the columns (use when columns of X are contiguous: consecutive
-// entries of a SASO/CSC-ordered operator touch consecutive rows of X).
-template <typename T, typename I>
-__global__ void __launch_bounds__(256) coo_scatter_cols_kernel(int64_t nnz, const I* __restrict__ rows, const I* __restrict__ cols,
-                                                              const T* __restrict__ vals, bool trans, int64_t ro, int64_t co,
-                                                              int64_t M, int64_t N, int64_t K, T alpha, const T* __restrict__ X,
-                                                              int64_t sx_l, int64_t sx_j, T* __restrict__ C, int64_t sc_i, int64_t sc_j,
-                                                              int64_t jchunk) {
-    const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= nnz) return;
-    const int64_t r = (int64_t) rows[e] - ro, c = (int64_t) cols[e] - co;
-    const int64_t i = trans ? c : r, l = trans ? r : c;
-    if (i < 0 || i >= M || l < 0 || l >= K) return;
-    const T v = alpha * vals[e];
-    const int64_t j0 = (int64_t) blockIdx.y * jchunk;
-    const int64_t j1 = (j0 + jchunk < N) ? j0 + jchunk : N;
-    for (int64_t j = j0; j < j1; ++j) atomicAdd(C + i * sc_i + j * sc_j, v * X[l * sx_l + j * sx_j]);
-}
-
-template <typename T, typename I>
-int launch_coo_scatter(int64_t nnz, const I* rows, const I* cols, const T* vals, bool trans, int64_t ro, int64_t co,
-                       int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
-                       T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
-    if (nnz <= 0 || M <= 0 || N <= 0 || K <= 0 || alpha == (T) 0) return RBX_OK;
-    if (sx_j <= sx_l) {
-        int64_t blocks = (nnz * 32 + 255) / 256;
-        if (blocks > kNumSMs * 32) blocks = kNumSMs * 32;
-        coo_scatter_rows_kernel<T, I><<<(unsigned) blocks, 256, 0, stream>>>(nnz, rows, cols, vals, trans, ro, co, M, N, K, alpha,
-                                                                           X, sx_l, sx_j, C, sc_i, sc_j);
-    } else {
-        const int64_t jchunk = 32;
-        dim3 grid((unsigned)((nnz + 255) / 256), (unsigned)((N + jchunk - 1) / jchunk));
-        if (grid.y > 65535u) return RBX_ERR_UNSUPPORTED;
-        coo_scatter_cols_kernel<T, I><<<grid, 256, 0, stream>>>(nnz, rows, cols, vals, trans, ro, co, M, N, K, alpha,
-                                                              X, sx_l, sx_j, C, sc_i, sc_j, jchunk);
-    }
-    count_launch();
-    return check_launch("coo_scatter_kernel");
-}
-#define RBX_INST_COO(T, I)                                                                                                     \
-    template int launch_coo_scatter<T, I>(int64_t, const I*, const I*, const T*, bool, int64_t, int64_t, int64_t, int64_t,      \
-                                          int64_t, T, const T*, int64_t, int64_t, T*, int64_t, int64_t, cudaStream_t);
-RBX_INST_COO(float, int32_t) RBX_INST_COO(float, int64_t) RBX_INST_COO(double, int32_t) RBX_INST_COO(double, int64_t)
-#undef RBX_INST_COO
-
-// Sparse data entry (p, q, v) contributes v * Sd[:, l] to C[:, j]; one warp per entry, lanes along i.
-template <typename T>
-__global__ void __launch_bounds__(256) spdata_scatter_kernel(int64_t nnz, const int64_t* __restrict__ prow, const int64_t* __restrict__ pcol,
-                                                            const T* __restrict__ vals, bool trans, int64_t ro, int64_t co,
-                                                            int64_t M, int64_t N, int64_t K, T alpha, const T* __restrict__ Sd,
-                                                            T* __restrict__ C, int64_t sc_i, int64_t sc_j) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
-    for (int64_t e = warp; e < nnz; e += nwarps) {
-        const int64_t p = prow[e] - ro, q = pcol[e] - co;
-        const int64_t l = trans ? q : p, j = trans ? p : q;
-        if (l < 0 || l >= K || j < 0 || j >= N) continue;
-        const T v = alpha * vals[e];
-        const T* s = Sd + l * M;
-        T* out = C + j * sc_j;
-        for (int64_t i = lane; i < M; i += 32) atomicAdd(out + i * sc_i, v * s[i]);
-    }
-}
-
-template <typename T>
-int launch_spdata_scatter(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
-                          int64_t M, int64_t N, int64_t K, T alpha, const T* Sd, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
-    if (nnz <= 0 || M <= 0 || N <= 0 || K <= 0 || alpha == (T) 0) return RBX_OK;
-    int64_t blocks = (nnz * 32 + 255) / 256;
-    if (blocks > kNumSMs * 32) blocks = kNumSMs * 32;
-    spdata_scatter_kernel<T><<<(unsigned) blocks, 256, 0, stream>>>(nnz, prow, pcol, vals, trans, ro, co, M, N, K, alpha, Sd, C, sc_i, sc_j);
-    count_launch();
-    return check_launch("spdata_scatter_kernel");
-}
-template int launch_spdata_scatter<float>(int64_t, const int64_t*, const int64_t*, const float*, bool, int64_t, int64_t, int64_t, int64_t,
-                                          int64_t, float, const float*, float*, int64_t, int64_t, cudaStream_t);
-template int launch_spdata_scatter<double>(int64_t, const int64_t*, const int64_t*, const double*, bool, int64_t, int64_t, int64_t, int64_t,
-                                           int64_t, double, const double*, double*, int64_t, int64_t, cudaStream_t);
-
 // dst[l * ldd + j] = src[l + j * lds]  (K x N): column-major data re-laid with contiguous rows, 64x64 tiles through smem
 template <typename T>
 __global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ src, int64_t K, int64_t N, int64_t lds, T* __restrict__ dst, int64_t ldd) {
@@ -178,5 +78,35 @@ int launch_expand_ptr(int64_t n_outer, const int64_t* ptr, int64_t* outer_idx, c
     count_launch();
     return check_launch("expand_ptr_kernel");
 }
+
+// util::require_symmetric (util.hh:165-188) on the device: |A_ij - A_ji| <= (|A_ij| + |A_ji| + 1) * tol for all i < j.
+// One thread per (i, j) pair of the strict upper triangle, tiles of 32 x 32 read through both orientations; *violated is
+// raised (never cleared) by any thread that finds a pair out of tolerance. NaNs never violate, as in the reference.
+template <typename T>
+__global__ void __launch_bounds__(256) require_symmetric_kernel(const T* __restrict__ A, int64_t n, int64_t s_row, int64_t s_col, T tol, int* violated) {
+    const int64_t tj = blockIdx.x, ti = blockIdx.y;
+    if (ti > tj) return;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int64_t i = ti * 32 + ty + 8 * r, j = tj * 32 + tx;
+        if (i < n && j < n && i < j) {
+            const T Aij = A[i * s_row + j * s_col], Aji = A[j * s_row + i * s_col];
+            const T viol = fabs(Aij - Aji), rel_tol = (fabs(Aij) + fabs(Aji) + (T) 1) * tol;
+            if (viol > rel_tol) *violated = 1;
+        }
+    }
+}
+template <typename T>
+int launch_require_symmetric(const T* A, int64_t n, int64_t s_row, int64_t s_col, T tol, int* violated_dev, cudaStream_t stream) {
+    if (n <= 1) return RBX_OK;
+    const int64_t nt = (n + 31) / 32;
+    if (nt > 65535) return RBX_ERR_UNSUPPORTED;
+    require_symmetric_kernel<T><<<dim3((unsigned) nt, (unsigned) nt), 256, 0, stream>>>(A, n, s_row, s_col, tol, violated_dev);
+    count_launch();
+    return check_launch("require_symmetric_kernel");
+}
+template int launch_require_symmetric<float>(const float*, int64_t, int64_t, int64_t, float, int*, cudaStream_t);
+template int launch_require_symmetric<double>(const double*, int64_t, int64_t, int64_t, double, int*, cudaStream_t);
 
 }  // namespace rbx

@@ -1,0 +1,169 @@
+// K4' general sparse-operator product, deterministic: C (M x N) = alpha * Sop (M x K) * X (K x N) + beta * C for an operator
+// given as COO triplets (an explicit or caller-edited SparseSkOp, a LASO, a tall operator, a SASO outside the streaming
+// kernel's envelope, left_spmm / right_spmm on a COO / CSR / CSC matrix).
+//
+// Replaces left_spmm -> coo::apply_coo_left_jki_p11 (spmm_dispatch.hh:48-160, coo_spmm_impl.hh:79-162), which sorts the
+// triplets on the host and walks them once per column of X. Round 1 scattered with atomicAdd (run-to-run different sums);
+// this is the output-stationary form:
+//   * the entries are regrouped by output row i on the device (count, scan, scatter, rank sort: the kernels of
+//     rbx_spdata.cu), each row cut into sub-segments by blocks of the contraction axis so that no sorted segment is long;
+//     within a row the entries come out in increasing l (duplicates ordered by their value bits);
+//   * rows of X contiguous: one warp owns 128 columns of one output row in registers and adds v * X[l, :] entry after entry
+//     (coalesced 128-byte reads, entry metadata fetched 32 at a time and broadcast by shuffles);
+//   * columns of X contiguous: one warp owns 4 columns of one output row; its lanes stride over the row's entries and the
+//     32 partial sums are folded by a butterfly in a fixed order;
+//   * alpha / beta are applied at the single store of each element (C is not read when beta == 0, util.hh:51-59).
+// No atomics, fixed summation order => bitwise reproducible. Roofline: HBM (nnz rows of X re-read; L2 absorbs what fits).
+#include "rbx_kernels.cuh"
+
+namespace rbx {
+
+template <typename T>
+struct CooGatherArgs {
+    const int64_t* ptr; const int64_t* lidx; const T* vals;     // sub-segments: row i owns [ptr[i * nlc], ptr[(i + 1) * nlc])
+    int64_t nlc;
+    int64_t M, N;
+    const T* X; int64_t sx_l, sx_j;
+    T alpha, beta;
+    T* C; int64_t sc_i, sc_j;
+};
+
+// rows of X contiguous (sx_j == 1; also the fallback for general strides): grid = (ceil(N / 128), ceil(M / WPB)); one warp
+// per (row i, 128-column tile), 4 accumulators per lane; the WPB warps of a block take consecutive rows of the same tile.
+constexpr int CG_WPB = 8;
+template <typename T>
+__global__ void __launch_bounds__(32 * CG_WPB) coo_gather_rows_kernel(const CooGatherArgs<T> a) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t i = (int64_t) blockIdx.y * CG_WPB + w;
+    if (i >= a.M) return;
+    const int64_t j0 = (int64_t) blockIdx.x * 128 + lane;
+    const int64_t beg = a.ptr[i * a.nlc], end = a.ptr[(i + 1) * a.nlc];
+    T acc[4] = { (T) 0, (T) 0, (T) 0, (T) 0 };
+    bool live[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) live[c] = j0 + 32 * c < a.N;
+    for (int64_t e0 = beg; e0 < end; e0 += 32) {
+        int64_t my_l = 0; T my_v = (T) 0;
+        if (e0 + lane < end) { my_l = a.lidx[e0 + lane]; my_v = a.vals[e0 + lane]; }
+        const int cnt = (end - e0 < 32) ? (int)(end - e0) : 32;
+        int u = 0;
+        for (; u + 4 <= cnt; u += 4) {                           // four entries in flight
+            T x[4][4], v[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int64_t l = __shfl_sync(0xffffffffu, my_l, u + q);
+                v[q] = __shfl_sync(0xffffffffu, my_v, u + q);
+                const T* row = a.X + l * a.sx_l + j0;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) x[q][c] = live[c] ? __ldg(row + 32 * c) : (T) 0;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[c] = fma(v[q], x[q][c], acc[c]);
+        }
+        for (; u < cnt; ++u) {
+            const int64_t l = __shfl_sync(0xffffffffu, my_l, u);
+            const T v = __shfl_sync(0xffffffffu, my_v, u);
+            const T* row = a.X + l * a.sx_l + j0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) if (live[c]) acc[c] = fma(v, __ldg(row + 32 * c), acc[c]);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+        if (live[c]) {
+            T* p = a.C + i * a.sc_i + (j0 + 32 * c) * a.sc_j;
+            const T r = a.alpha * acc[c];
+            *p = (a.beta == (T) 0) ? r : r + a.beta * (*p);
+        }
+}
+
+// columns of X contiguous (sx_l == 1): grid = (ceil(N / 4), ceil(M / WPB)); a warp owns (row i, 4 columns); lanes stride over
+// the entries (consecutive lanes read increasing l of the same column: the sectors of a sorted segment are shared)
+template <typename T>
+__global__ void __launch_bounds__(32 * CG_WPB) coo_gather_cols_kernel(const CooGatherArgs<T> a) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t i = (int64_t) blockIdx.y * CG_WPB + w;
+    if (i >= a.M) return;
+    const int64_t j0 = (int64_t) blockIdx.x * 4;
+    const int64_t beg = a.ptr[i * a.nlc], end = a.ptr[(i + 1) * a.nlc];
+    T acc[4] = { (T) 0, (T) 0, (T) 0, (T) 0 };
+    const int nj = (a.N - j0 < 4) ? (int)(a.N - j0) : 4;
+    for (int64_t e = beg + lane; e < end; e += 32) {
+        const int64_t l = a.lidx[e];
+        const T v = a.vals[e];
+        const T* col = a.X + l * a.sx_l + j0 * a.sx_j;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) if (c < nj) acc[c] = fma(v, __ldg(col + c * a.sx_j), acc[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);     // fixed butterfly: the same sum in every lane
+    if (lane < nj) {
+        T s = acc[0];
+        if (lane == 1) s = acc[1];
+        if (lane == 2) s = acc[2];
+        if (lane == 3) s = acc[3];
+        T* p = a.C + i * a.sc_i + (j0 + lane) * a.sc_j;
+        const T r = a.alpha * s;
+        *p = (a.beta == (T) 0) ? r : r + a.beta * (*p);
+    }
+}
+
+template <typename T>
+int launch_coo_gather(int64_t nnz, const int64_t* rows, const int64_t* cols, const T* vals, bool trans, int64_t ro, int64_t co,
+                      int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
+                      T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return RBX_OK;
+    if (alpha == (T) 0 || nnz <= 0 || K <= 0) return launch_scale_view<T>(C, M, N, sc_i, sc_j, beta, stream);
+    // sub-segments: aim at ~64 entries each (the rank sort works out of shared memory up to 256), at most 2^22 segments
+    int lc_shift = 62; int64_t nlc = 1;
+    const double per_row = (double) nnz / (double) M;
+    if (per_row > 128.0) {
+        int64_t want = (int64_t)(per_row / 64.0);
+        const int64_t cap = ((int64_t) 1 << 22) / (M > 0 ? M : 1);
+        if (want > cap) want = cap;
+        if (want < 1) want = 1;
+        int sh = 0;
+        while (((K + ((int64_t) 1 << sh) - 1) >> sh) > want) ++sh;
+        lc_shift = sh; nlc = (K + ((int64_t) 1 << sh) - 1) >> sh;
+        if (nlc < 1) nlc = 1;
+    }
+    // group by output row: the regroup kernels map (p, q) -> (l, j) = trans' ? (q - co, p - ro) : (p - ro, q - co) and
+    // group by j; here j must be the output row i, so trans' = !trans (see rbx_kernels.cuh)
+    int64_t *ptr = nullptr, *lidx = nullptr; T* v = nullptr;
+    int rc = spd_group_by_column<T>(nnz, rows, cols, vals, !trans, ro, co, K, M, &ptr, &lidx, &v, stream, lc_shift, nlc);
+    if (rc != RBX_OK) return rc;
+    CooGatherArgs<T> a;
+    a.ptr = ptr; a.lidx = lidx; a.vals = v; a.nlc = nlc; a.M = M; a.N = N; a.X = X; a.sx_l = sx_l; a.sx_j = sx_j;
+    a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j;
+    const int64_t by = (M + CG_WPB - 1) / CG_WPB;
+    // grid.y is limited to 65535: tile the rows in launches of that many blocks
+    for (int64_t y0 = 0; y0 < by && rc == RBX_OK; y0 += 65535) {
+        const int64_t ny = (by - y0 < 65535) ? by - y0 : 65535;
+        CooGatherArgs<T> b = a;
+        b.ptr = a.ptr + y0 * CG_WPB * nlc; b.M = (M - y0 * CG_WPB < ny * CG_WPB) ? M - y0 * CG_WPB : ny * CG_WPB;
+        b.C = a.C + y0 * CG_WPB * sc_i;
+        if (sx_j == 1 || sx_l != 1) {
+            const int64_t bx = (N + 127) / 128;
+            if (bx > 0x7fffffffLL) { rc = RBX_ERR_UNSUPPORTED; break; }
+            coo_gather_rows_kernel<T><<<dim3((unsigned) bx, (unsigned) ny), 32 * CG_WPB, 0, stream>>>(b);
+        } else {
+            const int64_t bx = (N + 3) / 4;
+            if (bx > 0x7fffffffLL) { rc = RBX_ERR_UNSUPPORTED; break; }
+            coo_gather_cols_kernel<T><<<dim3((unsigned) bx, (unsigned) ny), 32 * CG_WPB, 0, stream>>>(b);
+        }
+        count_launch();
+        rc = check_launch("coo_gather_kernel");
+    }
+    cudaFreeAsync(ptr, stream); cudaFreeAsync(lidx, stream); cudaFreeAsync(v, stream);
+    return rc;
+}
+template int launch_coo_gather<float>(int64_t, const int64_t*, const int64_t*, const float*, bool, int64_t, int64_t, int64_t, int64_t, int64_t,
+                                      float, const float*, int64_t, int64_t, float, float*, int64_t, int64_t, cudaStream_t);
+template int launch_coo_gather<double>(int64_t, const int64_t*, const int64_t*, const double*, bool, int64_t, int64_t, int64_t, int64_t, int64_t,
+                                       double, const double*, int64_t, int64_t, double, double*, int64_t, int64_t, cudaStream_t);
+
+}  // namespace rbx

@@ -10,7 +10,8 @@
 #include <cstring>
 #include <vector>
 #include <cmath>
-#include "RandBLAS_b200.hh"
+#include <sstream>
+#include <RandBLAS.hh>                       // the drop-in name: include/RandBLAS.hh forwards to RandBLAS_b200.hh
 
 extern "C" {
 int orc_fill_dense_f32(char, int64_t, int64_t, char, char, int64_t, int64_t, int64_t, int64_t, float*, const uint32_t*, const uint32_t*, uint32_t*);
@@ -53,16 +54,16 @@ static void test_fill_dense() {
                 std::vector<float> got(7 * cols), want(7 * cols);
                 RNGState<> next = fill_dense(D, got.data(), seed);
                 uint32_t nx[4];
-                CHECK(orc_fill_dense_f32(detail::ch(dist_to_layout(D)), 7, cols, (char) fam, (char) ma, 7, cols, 0, 0, want.data(), seed.counter, seed.key, nx) == 0);
+                CHECK(orc_fill_dense_f32(detail::ch(dist_to_layout(D)), 7, cols, (char) fam, (char) ma, 7, cols, 0, 0, want.data(), seed.counter.v, seed.key.v, nx) == 0);
                 CHECK(bits_equal(got, want));
-                CHECK(std::memcmp(next.counter, nx, 16) == 0);
+                CHECK(std::memcmp(next.counter.v, nx, 16) == 0);
                 DenseSkOp<float> S(D, seed);
-                CHECK(std::memcmp(S.next_state.counter, nx, 16) == 0);
+                CHECK(std::memcmp(S.next_state.counter.v, nx, 16) == 0);
                 // sub-matrix with offsets, both layouts, double
                 std::vector<double> g2(3 * 5), w2(3 * 5);
                 for (auto lay : { blas::Layout::ColMajor, blas::Layout::RowMajor }) {
                     fill_dense(lay, D, 3, 5, 2, 4, g2.data(), seed);
-                    CHECK(orc_fill_dense_f64(detail::ch(lay), 7, cols, (char) fam, (char) ma, 3, 5, 2, 4, w2.data(), seed.counter, seed.key, nx) == 0);
+                    CHECK(orc_fill_dense_f64(detail::ch(lay), 7, cols, (char) fam, (char) ma, 3, 5, 2, 4, w2.data(), seed.counter.v, seed.key.v, nx) == 0);
                     CHECK(bits_equal(g2, w2));
                 }
             }
@@ -72,7 +73,7 @@ static void test_fill_dense() {
     CHECK(S.buff != nullptr && S.del_buff_on_destruct);
     std::vector<double> want(240), got(S.buff, S.buff + 240);
     uint32_t nx[4];
-    orc_fill_dense_f64(detail::ch(S.layout), 6, 40, 'G', 'L', 6, 40, 0, 0, want.data(), S.seed_state.counter, S.seed_state.key, nx);
+    orc_fill_dense_f64(detail::ch(S.layout), 6, 40, 'G', 'L', 6, 40, 0, 0, want.data(), S.seed_state.counter.v, S.seed_state.key.v, nx);
     CHECK(bits_equal(got, want));
     bool threw = false;
     try { std::vector<float> b(4); fill_dense(DenseDist(2, 2, DenseDistName::BlackBox), b.data(), RNGState<>(0)); } catch (const std::invalid_argument&) { threw = true; }
@@ -87,13 +88,13 @@ static void test_fill_sparse() {
             fill_sparse(S);
             const int64_t n = nnz(S);
             std::vector<int64_t> r(n), c(n); std::vector<double> v(n); uint32_t nx[4];
-            CHECK(orc_fill_sparse_f64_i64(D.n_rows, D.n_cols, 3, (char) ma, S.seed_state.counter, S.seed_state.key, r.data(), c.data(), v.data(), nx) == 0);
+            CHECK(orc_fill_sparse_f64_i64(D.n_rows, D.n_cols, 3, (char) ma, S.seed_state.counter.v, S.seed_state.key.v, r.data(), c.data(), v.data(), nx) == 0);
             CHECK(std::memcmp(r.data(), S.rows, n * 8) == 0 && std::memcmp(c.data(), S.cols, n * 8) == 0 && std::memcmp(v.data(), S.vals, n * 8) == 0);
-            CHECK(std::memcmp(nx, S.next_state.counter, 16) == 0);
+            CHECK(std::memcmp(nx, S.next_state.counter.v, 16) == 0);
             SparseSkOp<float, r123::Philox4x32, int32_t> S32(D, 99);
             fill_sparse(S32);
             std::vector<int32_t> r32(n), c32(n); std::vector<float> v32(n);
-            CHECK(orc_fill_sparse_f32_i32(D.n_rows, D.n_cols, 3, (char) ma, S32.seed_state.counter, S32.seed_state.key, r32.data(), c32.data(), v32.data(), nx) == 0);
+            CHECK(orc_fill_sparse_f32_i32(D.n_rows, D.n_cols, 3, (char) ma, S32.seed_state.counter.v, S32.seed_state.key.v, r32.data(), c32.data(), v32.data(), nx) == 0);
             CHECK(std::memcmp(r32.data(), S32.rows, n * 4) == 0 && std::memcmp(c32.data(), S32.cols, n * 4) == 0 && std::memcmp(v32.data(), S32.vals, n * 4) == 0);
         }
 }
@@ -112,13 +113,13 @@ static void test_sketch_dense() {
         const int64_t lda = lay == blas::Layout::ColMajor ? m : n, ldb = lay == blas::Layout::ColMajor ? d : n;
         std::vector<double> B(d * n, 0.5), W(d * n, 0.5);
         sketch_general(lay, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.5, S, A.data(), lda, -0.5, B.data(), ldb);
-        CHECK(orc_sketch_dense_f64('L', detail::ch(lay), 'N', 'N', d, n, m, 1.5, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, A.data(), lda, -0.5, W.data(), ldb) == 0);
+        CHECK(orc_sketch_dense_f64('L', detail::ch(lay), 'N', 'N', d, n, m, 1.5, d, m, 'G', 'L', S.seed_state.counter.v, S.seed_state.key.v, 0, 0, A.data(), lda, -0.5, W.data(), ldb) == 0);
         CHECK(max_rel(B, W) < 1e-13);
         // right sketch with the transposed operator: B (n x d) = A^T (n x m) * S^T (m x d)
         const int64_t ldb2 = lay == blas::Layout::ColMajor ? n : d;
         std::vector<double> B2(n * d, 0.0), W2(n * d, 0.0);
         sketch_general(lay, blas::Op::Trans, blas::Op::Trans, n, d, m, 1.0, A.data(), lda, S, 0.0, B2.data(), ldb2);
-        CHECK(orc_sketch_dense_f64('R', detail::ch(lay), 'T', 'T', n, d, m, 1.0, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, A.data(), lda, 0.0, W2.data(), ldb2) == 0);
+        CHECK(orc_sketch_dense_f64('R', detail::ch(lay), 'T', 'T', n, d, m, 1.0, d, m, 'G', 'L', S.seed_state.counter.v, S.seed_state.key.v, 0, 0, A.data(), lda, 0.0, W2.data(), ldb2) == 0);
         CHECK(max_rel(B2, W2) < 1e-13);
     }
     // explicit buffer == implicit operator
@@ -131,7 +132,7 @@ static void test_sketch_dense() {
     // sketch_vector and dimension checks
     std::vector<double> x = randmat(m, 5), y(d, 0.0), wy(d, 0.0);
     sketch_vector(blas::Op::NoTrans, 1.0, S, x.data(), 1, 0.0, y.data(), 1);
-    orc_sketch_dense_f64('L', 'R', 'N', 'N', d, 1, m, 1.0, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, x.data(), 1, 0.0, wy.data(), 1);
+    orc_sketch_dense_f64('L', 'R', 'N', 'N', d, 1, m, 1.0, d, m, 'G', 'L', S.seed_state.counter.v, S.seed_state.key.v, 0, 0, x.data(), 1, 0.0, wy.data(), 1);
     CHECK(max_rel(y, wy) < 1e-13);
     bool threw = false;
     try { sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d + 1, n, m, 1.0, S, A.data(), m, 0.0, B.data(), d + 1); } catch (const Error&) { threw = true; }
@@ -144,7 +145,7 @@ static void test_sketch_dense() {
     std::vector<float> Af(m * n), Bf(d * n, 0.f), Wf(d * n, 0.f);
     fill_dense(DenseDist(m, n), Af.data(), RNGState<>(99));
     sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.f, Sf, Af.data(), m, 0.f, Bf.data(), d);
-    orc_sketch_dense_f32('L', 'C', 'N', 'N', d, n, m, 1.f, d, m, 'U', 'L', Sf.seed_state.counter, Sf.seed_state.key, 0, 0, Af.data(), m, 0.f, Wf.data(), d);
+    orc_sketch_dense_f32('L', 'C', 'N', 'N', d, n, m, 1.f, d, m, 'U', 'L', Sf.seed_state.counter.v, Sf.seed_state.key.v, 0, 0, Af.data(), m, 0.f, Wf.data(), d);
     CHECK(max_rel(Bf, Wf) < 1e-5);
 }
 
@@ -156,7 +157,7 @@ static void test_sketch_sparseop() {
         SparseSkOp<double> S({ d, m, 8, MajorAxis::Short }, 1997);
         std::vector<double> B(d * n, 0.0), W(d * n, 0.0), B2(d * n, 0.0);
         sketch_general(lay, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, A.data(), lda, 0.0, B.data(), ldb);     // implicit (streaming kernel)
-        CHECK(orc_sketch_sparseop_f64('L', detail::ch(lay), 'N', 'N', d, n, m, 1.0, d, m, 8, 'S', S.seed_state.counter, S.seed_state.key, 0, 0, A.data(), lda, 0.0, W.data(), ldb) == 0);
+        CHECK(orc_sketch_sparseop_f64('L', detail::ch(lay), 'N', 'N', d, n, m, 1.0, d, m, 8, 'S', S.seed_state.counter.v, S.seed_state.key.v, 0, 0, A.data(), lda, 0.0, W.data(), ldb) == 0);
         CHECK(max_rel(B, W) < 1e-13);
         fill_sparse(S);                                                                                                       // explicit triplets
         sketch_general(lay, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, A.data(), lda, 0.0, B2.data(), ldb);
@@ -169,7 +170,7 @@ static void test_sketch_sparseop() {
     SparseSkOp<double> SL({ ns, ds, 2, MajorAxis::Long }, 5);
     std::vector<double> B(ns * ds, 0.0), W(ns * ds, 0.0);
     sketch_symmetric(blas::Layout::ColMajor, 1.0, Sym.data(), ns, SL, 0.0, B.data(), ns);
-    orc_sketch_sparseop_f64('R', 'C', 'N', 'N', ns, ds, ns, 1.0, ns, ds, 2, 'L', SL.seed_state.counter, SL.seed_state.key, 0, 0, Sym.data(), ns, 0.0, W.data(), ns);
+    orc_sketch_sparseop_f64('R', 'C', 'N', 'N', ns, ds, ns, 1.0, ns, ds, 2, 'L', SL.seed_state.counter.v, SL.seed_state.key.v, 0, 0, Sym.data(), ns, 0.0, W.data(), ns);
     CHECK(max_rel(B, W) < 1e-13);
     Sym[1] += 1.0;
     bool threw = false;
@@ -188,7 +189,7 @@ static void test_sketch_sparse() {
     DenseSkOp<double> S(DenseDist(d, m), 0);
     std::vector<double> B(d * n, 0.0), W(d * n, 0.0);
     sketch_sparse(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, 0, 0, A, 0, 0, 0.0, B.data(), d);
-    CHECK(orc_sketch_sparsedata_f64('L', 'C', 'N', 'N', d, n, m, 1.0, d, m, 'G', 'L', S.seed_state.counter, S.seed_state.key, 0, 0, 'R', m, n, A.nnz,
+    CHECK(orc_sketch_sparsedata_f64('L', 'C', 'N', 'N', d, n, m, 1.0, d, m, 'G', 'L', S.seed_state.counter.v, S.seed_state.key.v, 0, 0, 'R', m, n, A.nnz,
                                     A.vals, A.rowptr, A.colidxs, 0, 0, 0.0, W.data(), d) == 0);
     CHECK(max_rel(B, W) < 1e-13);
 }
@@ -206,15 +207,87 @@ static void test_index_sampling() {
     std::vector<int64_t> got(k), want(k);
     uint32_t next[4];
     RNGState<> out = util::sample_indices_iid(n, w.data(), k, got.data(), st);
-    orc_sample_indices_iid_f64(n, cdf.data(), k, want.data(), st.counter, st.key, next);
-    CHECK(got == want && std::memcmp(out.counter, next, 16) == 0);
+    orc_sample_indices_iid_f64(n, cdf.data(), k, want.data(), st.counter.v, st.key.v, next);
+    CHECK(got == want && std::memcmp(out.counter.v, next, 16) == 0);
     out = util::sample_indices_iid_uniform(n, k, got.data(), st);
-    orc_sample_indices_iid_uniform(n, k, want.data(), st.counter, st.key, next);
-    CHECK(got == want && std::memcmp(out.counter, next, 16) == 0);
+    orc_sample_indices_iid_uniform(n, k, want.data(), st.counter.v, st.key.v, next);
+    CHECK(got == want && std::memcmp(out.counter.v, next, 16) == 0);
     bool threw = false;
     std::vector<double> bad = { 0.5, -0.1, 0.5 };
     try { util::weights_to_cdf(3, bad.data()); } catch (const Error&) { threw = true; }
     CHECK(threw);
+}
+
+
+// base.hh:161-251: RNGState with Random123-style arrays (what INTEGRATION.md's stub and reference callers touch)
+static void test_rngstate_surface() {
+    RNGState<> s(7);
+    CHECK(s.key[0] == 7 && s.key.v[1] == 0 && s.counter.v[0] == 0 && RNGState<>::len_c == 4 && RNGState<>::len_k == 2);
+    s.counter.v[0] = 0xFFFFFFFFu; s.counter.v[1] = 0xFFFFFFFFu;
+    s.counter.incr(1);                                            // carry across two words (test_r123.cc:679-766)
+    CHECK(s.counter[0] == 0 && s.counter[1] == 0 && s.counter[2] == 1 && s.counter[3] == 0);
+    uint32_t c2[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0 };
+    rbx_ctr_add(c2, 1);
+    CHECK(std::memcmp(c2, s.counter.v, 16) == 0);
+    s.counter.incr(0x100000005ull);
+    CHECK(s.counter[0] == 5 && s.counter[1] == 1 && s.counter[2] == 1);
+    RNGState<> t = s;                                             // copies (base.hh:217-232)
+    CHECK(t.counter == s.counter && t.key == s.key);
+    s.key.incr(3);
+    CHECK(s.key[0] == 10 && t.key[0] == 7);
+    std::ostringstream os; os << t;
+    CHECK(os.str() == "counter : {5, 1, 1, 0}\nkey     : {7, 0}");
+}
+
+// sparse_skops.hh:484-513 and spmm_dispatch.hh / conversions.hh: views, transposes, conversions and the public SpMM
+static void test_sparse_surface() {
+    const int64_t d = 12, m = 90, n = 7;
+    SparseDist D = { d, m, 3, MajorAxis::Short };
+    SparseSkOp<double> S(D, RNGState<>(5));
+    auto Sv = coo_view_of_skop(S);                                // fills S
+    CHECK(S.known_filled && Sv.nnz == 3 * m && Sv.rows == S.rows && !Sv.own_memory);
+    auto St = transpose(S);
+    CHECK(St.dist.n_rows == m && St.dist.n_cols == d && St.rows == S.cols && St.cols == S.rows && St.known_filled && !St.own_memory);
+    std::vector<double> A(m * n), B1(d * n, 0.0), B2(d * n, 0.0), B3(d * n, 0.0), W(d * n, 0.0);
+    for (size_t i = 0; i < A.size(); ++i) A[i] = std::sin(0.37 * i);
+    orc_sketch_sparseop_f64('L', 'C', 'N', 'N', d, n, m, 1.0, d, m, 3, 'S', S.seed_state.counter.v, S.seed_state.key.v, 0, 0, A.data(), m, 0.0, W.data(), d);
+    left_spmm(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, Sv, 0, 0, A.data(), m, 0.0, B1.data(), d);
+    CHECK(max_rel(B1, W) < 1e-13);
+    sketch_general(blas::Layout::ColMajor, blas::Op::Trans, blas::Op::NoTrans, d, n, m, 1.0, St, A.data(), m, 0.0, B2.data(), d);     // S^T transposed back
+    CHECK(max_rel(B2, W) < 1e-13);
+    // COO -> CSR / CSC on the device, then the same product through each format and through right_spmm
+    sparse_data::CSRMatrix<double> R(d, m); sparse_data::CSCMatrix<double> C(d, m);
+    sparse_data::conversions::coo_to_csr(Sv, R);
+    sparse_data::conversions::coo_to_csc(Sv, C);
+    CHECK(R.nnz == Sv.nnz && C.nnz == Sv.nnz && R.rowptr[0] == 0 && R.rowptr[d] == Sv.nnz && C.colptr[m] == Sv.nnz);
+    bool sorted = true;
+    for (int64_t i = 0; i < d; ++i) for (int64_t e = R.rowptr[i] + 1; e < R.rowptr[i + 1]; ++e) sorted = sorted && R.colidxs[e - 1] < R.colidxs[e];
+    for (int64_t j = 0; j < m; ++j) { CHECK(C.colptr[j + 1] - C.colptr[j] == 3); for (int64_t e = C.colptr[j] + 1; e < C.colptr[j + 1]; ++e) sorted = sorted && C.rowidxs[e - 1] < C.rowidxs[e]; }
+    CHECK(sorted);
+    left_spmm(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, R, 0, 0, A.data(), m, 0.0, B3.data(), d);
+    CHECK(max_rel(B3, W) < 1e-13);
+    std::fill(B3.begin(), B3.end(), 0.0);
+    spmm(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, C, 0, 0, A.data(), m, 0.0, B3.data(), d);
+    CHECK(max_rel(B3, W) < 1e-13);
+    auto Ct = sparse_data::conversions::transpose_as_csr(C);     // zero-copy: C^T as CSR (m x d)
+    CHECK(Ct.n_rows == m && Ct.n_cols == d && Ct.rowptr == C.colptr && Ct.colidxs == C.rowidxs);
+    // right_spmm: Bt (n x d) = At (n x m) * S^T (m x d), RowMajor buffers are the ColMajor ones transposed
+    std::vector<double> Bt(n * d, 0.0);
+    right_spmm(blas::Layout::RowMajor, blas::Op::NoTrans, blas::Op::NoTrans, n, d, m, 1.0, A.data(), m, Ct, 0, 0, 0.0, Bt.data(), d);
+    CHECK(max_rel(Bt, W) < 1e-13);
+    sparse_data::COOMatrix<double> back(d, m);
+    sparse_data::conversions::csr_to_coo(R, back);
+    CHECK(back.nnz == Sv.nnz && back.sort == sparse_data::NonzeroSort::CSR && back.rows[0] == 0);
+    // host-pointer sketch into a window of a larger B (ldb > d) with beta == 0: the padding survives
+    const int64_t ldb = d + 5;
+    std::vector<double> Bp(ldb * n, -7.0);
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S, (int64_t) 0, (int64_t) 0, A.data(), m, 0.0, Bp.data(), ldb);
+    bool pad_ok = true, val_ok = true;
+    for (int64_t j = 0; j < n; ++j) for (int64_t i = 0; i < ldb; ++i) {
+        if (i >= d) { if (j < n - 1 || i < d) pad_ok = pad_ok && Bp[i + j * ldb] == -7.0; }
+        else val_ok = val_ok && std::abs(Bp[i + j * ldb] - W[i + j * d]) <= 1e-12 * (1 + std::abs(W[i + j * d]));
+    }
+    CHECK(pad_ok && val_ok);
 }
 
 int main() {
@@ -225,6 +298,8 @@ int main() {
     test_sketch_sparseop();
     test_sketch_sparse();
     test_index_sampling();
+    test_rngstate_surface();
+    test_sparse_surface();
     std::printf(failures ? "FAILED (%d)\n" : "OK\n", failures);
     return failures ? 1 : 0;
 }

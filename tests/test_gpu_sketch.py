@@ -308,6 +308,41 @@ def test_saso_tail_paths(rb, cuda, dt, monkeypatch):
     monkeypatch.delenv("RBX_SASO_CAP", raising=False)
 
 
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_general_sparse_operator_path_is_deterministic(rb, cuda, dt):
+    """LASO, tall operators, explicit (filled) triplets and vec_nnz > 32 run the output-stationary gather of
+    rbx_spmm_gather.cu (no atomics): correct against the oracle -- including rows long enough to be cut into sub-segments --
+    and bit-identical from run to run, for both layouts of the data."""
+    for layout in "CR":
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 24, 70, 20000, 1.5, -0.5, 6, "L", key=5)         # LASO, 5000 entries per row
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 64, 33, 6000, 1.0, 0.0, 40, "S", key=5)          # vec_nnz > 32
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 300, 140, 40, 1.0, 0.5, 3, "S", key=5)           # tall S (lift)
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 16, 130, 9000, 2.0, 0.0, 4, "S", key=5, filled=True)
+    npdt = np.float32 if dt == "f32" else np.float64
+    rng = np.random.default_rng(1)
+    for (d, n, m, k, ma, layout) in [(24, 70, 20000, 6, "L", "C"), (24, 70, 20000, 6, "L", "R"), (64, 33, 6000, 40, "S", "R")]:
+        A = torch.from_numpy(rng.standard_normal(m * n).astype(npdt)).to(cuda)
+        S = rb.SparseSkOp(rb.SparseDist(d, m, k, ma), 11, dtype=TDT[dt])
+        lda, ldb = (m, d) if layout == "C" else (n, n)
+        outs = []
+        for _ in range(3):
+            B = torch.zeros(d * n, dtype=TDT[dt], device=cuda)
+            rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A, lda, 0.0, B, ldb)
+            outs.append(B)
+        assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2]), (d, n, m, k, ma, layout)
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_saso_windows_up_to_8192_rows_take_the_streaming_kernel(rb, cuda, dt):
+    """operator windows of 4097..8192 rows (5 to 8 row blocks of the tile kernel): same result as the definition, and the launch
+    count shows the streaming kernel ran (prep + two tile variants [+ reduce]), not fill_sparse + regroup + gather"""
+    for layout in "CR":
+        l0 = rb.lib.rbx_launch_count()
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 5000, 40, 12000, 1.0, 0.0, 8, "S", key=9)
+        assert rb.lib.rbx_launch_count() - l0 <= 4
+        run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", 8192, 24, 9000, 1.5, -1.0, 8, "S", key=9)
+
+
 # ---------------------------------------------------------------------------------------------- sparse data
 def random_sparse(rng, rows, cols, density, npdt):
     M = rng.standard_normal((rows, cols)) * (rng.random((rows, cols)) < density)
