@@ -492,16 +492,64 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
         if (rc != RBX_OK) return rc;
         seg_ptr = own_ptr; seg_l = own_l; seg_v = own_v;
     }
-    // the operator window is generated in slabs of the contraction axis, as floats, Mp x Ks at a time (i contiguous)
+    const int64_t ma = major_axis_length(D_rows, D_cols, major_axis);
     const int64_t Mp = (s.M + 3) & ~(int64_t) 3;
+    float* Sd = nullptr;
+    // Two schedules. (1) One pass over the nonzeros, each gathering a full column of the float operator window
+    // (spdata_gather_kernel): when the window (4 * Mp * K bytes) is far larger than L2 every gather is an HBM miss --
+    // 198 GB of DRAM reads at C4, 36.4 ms. (2) RBX_SPD_DC = 8 / 16 / 32: the OUTPUT rows are blocked, dc at a time, with a
+    // dc x K float slab (64 MB at C4 for dc = 16) generated per pass and kept in L2 (evict_last) while the nonzeros stream
+    // through (evict_first). Measured at C4 (profiles/r02_c4_row_blocked_ncu.csv): DRAM reads fall to 81 GB, but the
+    // gathers now run at the L2's bandwidth instead -- 407 GB of L2 traffic at 10.9 TB/s = 37.3 ms for the 32 passes, the
+    // same time -- because with random sparsity nothing is reused above L2: nnz * 4 * M bytes must reach the SMs either
+    // way. Schedule (1) therefore stays the default; (2) is kept, tested, for operators whose window exceeds device memory.
+    int dc = 0;
+    if (const char* ev = getenv("RBX_SPD_DC")) { const int v = atoi(ev); dc = (v == 8 || v == 16 || v == 32) ? v : 0; }
+    if (dc == 0 && (double) Mp * (double) s.K * 4.0 > 0.5 * (double) ws_budget(~(size_t) 0 >> 1) * 4.0) dc = 16;   // window beyond half the free memory
+    if (dc > 0) {
+        float* slab[2] = { nullptr, nullptr };
+        const size_t slab_bytes = 4 * (size_t) dc * (size_t) s.K;
+        cudaStream_t aux = aux_stream();
+        cudaEvent_t filled[2] = { nullptr, nullptr }, used[2] = { nullptr, nullptr };
+        bool ok = ws_alloc(&slab[0], slab_bytes, st) == cudaSuccess && ws_alloc(&slab[1], slab_bytes, st) == cudaSuccess && aux != nullptr;
+        for (int b = 0; b < 2 && ok; ++b)
+            ok = cudaEventCreateWithFlags(&filled[b], cudaEventDisableTiming) == cudaSuccess && cudaEventCreateWithFlags(&used[b], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
+        // the slab of pass p + 1 is generated on the auxiliary stream while pass p gathers
+        auto fill = [&](int64_t i0, int b, cudaStream_t fs) -> int {
+            const int64_t rows = (s.M - i0 < dc) ? s.M - i0 : dc;
+            if (l_on_cols) return launch_fill_window<float>(family, ma, slab[b], rows, s.K, w.pr0 + i0, w.pc0, w.ctr, w.key, 1, dc, false, fs);
+            return launch_fill_window<float>(family, ma, slab[b], s.K, rows, w.pr0, w.pc0 + i0, w.ctr, w.key, dc, 1, false, fs);
+        };
+        if (rc == RBX_OK && cudaEventRecord(used[0], st) != cudaSuccess) rc = RBX_ERR_CUDA;       // orders the first fill after the allocations
+        if (rc == RBX_OK && cudaStreamWaitEvent(aux, used[0], 0) != cudaSuccess) rc = RBX_ERR_CUDA;
+        if (rc == RBX_OK) rc = fill(0, 0, aux);
+        if (rc == RBX_OK && cudaEventRecord(filled[0], aux) != cudaSuccess) rc = RBX_ERR_CUDA;
+        int64_t pass = 0;
+        for (int64_t i0 = 0; i0 < s.M && rc == RBX_OK; i0 += dc, ++pass) {
+            const int b = (int)(pass & 1), nb = b ^ 1;
+            const int64_t rows = (s.M - i0 < dc) ? s.M - i0 : dc;
+            if (i0 + dc < s.M) {                       // next slab: after the gather that last read that buffer
+                if (pass >= 1 && cudaStreamWaitEvent(aux, used[nb], 0) != cudaSuccess) rc = RBX_ERR_CUDA;
+                if (rc == RBX_OK) rc = fill(i0 + dc, nb, aux);
+                if (rc == RBX_OK && cudaEventRecord(filled[nb], aux) != cudaSuccess) rc = RBX_ERR_CUDA;
+            }
+            if (rc == RBX_OK && cudaStreamWaitEvent(st, filled[b], 0) != cudaSuccess) rc = RBX_ERR_CUDA;
+            if (rc == RBX_OK) rc = launch_spdata_gather_narrow<T>(s.N, seg_ptr, seg_l, seg_v, s.K, (int) rows, dc, slab[b], family == 'U', alpha, beta,
+                                                                 B + i0 * s.sc_i, s.sc_i, s.sc_j, st);
+            if (rc == RBX_OK && cudaEventRecord(used[b], st) != cudaSuccess) rc = RBX_ERR_CUDA;
+        }
+        if (aux && cudaEventRecord(used[0], aux) == cudaSuccess) cudaStreamWaitEvent(st, used[0], 0);   // the caller's stream outlives the aux work
+        for (int b = 0; b < 2; ++b) { if (filled[b]) cudaEventDestroy(filled[b]); if (used[b]) cudaEventDestroy(used[b]); if (slab[b]) cudaFreeAsync(slab[b], st); }
+        if (rc != RBX_OK) cudaGetLastError();
+    } else {
+    // the operator window is generated in slabs of the contraction axis, as floats, Mp x Ks at a time (i contiguous)
     const int64_t budget = (int64_t) ws_budget((size_t) 4 << 30);       // at most 4 GiB, at most a quarter of the free memory
     int64_t Ks = budget / (4 * Mp);
     if (const char* ev = getenv("RBX_SPD_SLAB")) { const int64_t v = atoll(ev); if (v >= 1) Ks = v; }
     if (Ks < 1) Ks = 1;
     if (Ks > s.K) Ks = s.K;
-    float* Sd = nullptr;
     if (ws_alloc(&Sd, 4 * (size_t)(Mp * Ks), st) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
-    const int64_t ma = major_axis_length(D_rows, D_cols, major_axis);
     for (int64_t l0 = 0; l0 < s.K && rc == RBX_OK; l0 += Ks) {
         const int64_t kk = (s.K - l0 < Ks) ? s.K - l0 : Ks;
         // unscaled floats: the uniform family's sqrt(3) is applied in T precision by the gather kernel
@@ -510,6 +558,7 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
         if (rc != RBX_OK) break;
         rc = launch_spdata_gather<T>(s.N, seg_ptr, seg_l, seg_v, l0, kk, s.M, Mp, Sd, family == 'U', l0 == 0, alpha, beta, B,
                                      s.sc_i, s.sc_j, st);
+    }
     }
     if (Sd) cudaFreeAsync(Sd, st);
     if (own_ptr) cudaFreeAsync(own_ptr, st);

@@ -61,6 +61,11 @@ int launch_require_symmetric(const T* A, int64_t n, int64_t s_row, int64_t s_col
 template <typename T>
 int launch_spdata_gather(int64_t N, const int64_t* ptr, const int64_t* lidx, const T* vals, int64_t l0, int64_t kk, int64_t M, int64_t Mp,
                          const float* Sd, bool uniform, bool first, T alpha, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+// the same product for `rows` <= dc output rows whose operator slab Sd[l * dc + i] (dc in {8, 16, 32}) is small enough to stay
+// in L2 while the nonzeros stream through (d-blocked passes of sketch_sparse); applies alpha / beta at its single store
+template <typename T>
+int launch_spdata_gather_narrow(int64_t N, const int64_t* ptr, const int64_t* lidx, const T* vals, int64_t K, int rows, int dc, const float* Sd,
+                                bool uniform, T alpha, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
 // regroup per-nonzero (p, q, v) into column segments of op(A) (sorted by l inside a segment). The three outputs are
 // stream-ordered allocations the caller releases with cudaFreeAsync.
 template <typename T>

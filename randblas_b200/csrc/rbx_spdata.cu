@@ -251,6 +251,118 @@ int launch_spdata_gather(int64_t N, const int64_t* ptr, const int64_t* lidx, con
     return check_launch("spdata_gather_kernel");
 }
 
+// ---- the gather kernel for an L2-resident operator slab (d-blocked passes) ----------------------------------------------
+// When the whole operator window (4 * M * K bytes as floats) is far larger than L2, every nonzero's gather of M floats is an
+// HBM miss (C4 round 1: 198 GB of DRAM reads against 5.7 GB of compulsory bytes). Here the OUTPUT rows are blocked instead:
+// one pass handles DC rows of C (DC = 16: a slab of 16 x K floats = 64 MB at C4), generates just those rows of the operator
+// (l-major, DC floats = 64 bytes per contraction index) and re-streams the nonzeros of op(A); the slab stays in L2 across
+// the pass (evict_last policy), the nonzeros are read with evict_first, C is written once (streaming stores). DRAM traffic
+// becomes (M / DC) * nnz * 16 + slab + C instead of nnz * 4 * M.
+// Mapping: DC / 4 lanes per nonzero (one float4 of operator rows each), 32 / (DC / 4) nonzeros per warp step, U steps in
+// flight; the per-group partial sums are folded by a fixed butterfly => bitwise reproducible.
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+    unsigned long long p; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+__device__ __forceinline__ unsigned long long l2_policy_evict_first() {
+    unsigned long long p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+__device__ __forceinline__ float4 ldg_f4_hint(const float* p, unsigned long long pol) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ unsigned long long ldg_u64_hint(const void* p, unsigned long long pol) {
+    unsigned long long v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+    return v;
+}
+template <typename T> __device__ __forceinline__ T ldg_val_hint(const T* p, unsigned long long pol);
+template <> __device__ __forceinline__ double ldg_val_hint<double>(const double* p, unsigned long long pol) { return __longlong_as_double((long long) ldg_u64_hint(p, pol)); }
+template <> __device__ __forceinline__ float ldg_val_hint<float>(const float* p, unsigned long long pol) {
+    float v; asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol)); return v;
+}
+
+struct SpdNarrowArgs {
+    int64_t N; const int64_t* ptr; const int64_t* lidx;
+    int64_t K;
+    int rows;                                              // live rows of this pass (<= DC)
+    const float* Sd;                                       // Sd[l * DC + i]
+    int64_t sc_i, sc_j;
+};
+
+template <typename T, int DC, bool UNI>
+__global__ void __launch_bounds__(256) spdata_gather_narrow_kernel(const SpdNarrowArgs a, const T* __restrict__ vals, T alpha, T beta, T* __restrict__ C) {
+    constexpr int LPE = DC / 4, EPW = 32 / LPE, U = 4;
+    const int lane = threadIdx.x & 31, g = lane / LPE, sub = lane % LPE;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    const unsigned long long keep = l2_policy_evict_last(), stream_once = l2_policy_evict_first();
+    const float* sd = a.Sd + sub * 4;
+    for (int64_t j = warp; j < a.N; j += nwarps) {
+        const int64_t beg = a.ptr[j], end = a.ptr[j + 1];
+        T acc[4] = { (T) 0, (T) 0, (T) 0, (T) 0 };
+        for (int64_t e0 = beg + g; e0 < end; e0 += EPW * U) {
+            int64_t l[U]; T v[U]; float4 s[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t e = e0 + (int64_t) u * EPW;
+                const bool in = e < end;
+                l[u] = in ? (int64_t) ldg_u64_hint(a.lidx + e, stream_once) : 0;
+                v[u] = in ? ldg_val_hint<T>(vals + e, stream_once) : (T) 0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) s[u] = ldg_f4_hint(sd + l[u] * DC, keep);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                acc[0] = fma(v[u], spd_value<T>(s[u].x, UNI), acc[0]);
+                acc[1] = fma(v[u], spd_value<T>(s[u].y, UNI), acc[1]);
+                acc[2] = fma(v[u], spd_value<T>(s[u].z, UNI), acc[2]);
+                acc[3] = fma(v[u], spd_value<T>(s[u].w, UNI), acc[3]);
+            }
+        }
+#pragma unroll
+        for (int o = LPE; o < 32; o <<= 1)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
+        if (g == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int i = sub * 4 + q;
+                if (i < a.rows) {
+                    T* p = C + i * a.sc_i + j * a.sc_j;
+                    const T r = alpha * acc[q];
+                    *p = (beta == (T) 0) ? r : r + beta * (*p);      // beta == 0: C is not read
+                }
+            }
+        }
+    }
+}
+
+template <typename T>
+int launch_spdata_gather_narrow(int64_t N, const int64_t* ptr, const int64_t* lidx, const T* vals, int64_t K, int rows, int dc, const float* Sd,
+                                bool uniform, T alpha, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
+    if (N <= 0 || rows <= 0) return RBX_OK;
+    if (dc != 16 && dc != 8 && dc != 32) return RBX_ERR_UNSUPPORTED;
+    SpdNarrowArgs a;
+    a.N = N; a.ptr = ptr; a.lidx = lidx; a.K = K; a.rows = rows; a.Sd = Sd; a.sc_i = sc_i; a.sc_j = sc_j;
+    int64_t bx = (N + 7) / 8;
+    const int64_t cap = (int64_t) kNumSMs * 8 * 2;
+    if (bx > cap) bx = cap;
+#define RBX_NARROW(DCV)                                                                                                          \
+    if (dc == DCV) {                                                                                                             \
+        if (uniform) spdata_gather_narrow_kernel<T, DCV, true><<<(unsigned) bx, 256, 0, stream>>>(a, vals, alpha, beta, C);        \
+        else         spdata_gather_narrow_kernel<T, DCV, false><<<(unsigned) bx, 256, 0, stream>>>(a, vals, alpha, beta, C);       \
+    }
+    RBX_NARROW(8) RBX_NARROW(16) RBX_NARROW(32)
+#undef RBX_NARROW
+    count_launch();
+    return check_launch("spdata_gather_narrow_kernel");
+}
+template int launch_spdata_gather_narrow<float>(int64_t, const int64_t*, const int64_t*, const float*, int64_t, int, int, const float*, bool, float, float,
+                                                float*, int64_t, int64_t, cudaStream_t);
+template int launch_spdata_gather_narrow<double>(int64_t, const int64_t*, const int64_t*, const double*, int64_t, int, int, const float*, bool, double, double,
+                                                 double*, int64_t, int64_t, cudaStream_t);
+
 template <typename T>
 int spd_group_by_column(int64_t nnz, const int64_t* prow, const int64_t* pcol, const T* vals, bool trans, int64_t ro, int64_t co,
                         int64_t K, int64_t N_cols, int64_t** ptr_out, int64_t** lidx_out, T** vals_out, cudaStream_t stream,

@@ -308,6 +308,30 @@ def test_saso_tail_paths(rb, cuda, dt, monkeypatch):
     monkeypatch.delenv("RBX_SASO_CAP", raising=False)
 
 
+@pytest.mark.parametrize("fmt", ["O", "R", "C"])
+@pytest.mark.parametrize("dc", ["8", "16", "32"])
+def test_sketch_sparse_row_blocked_passes(rb, cuda, fmt, dc, monkeypatch):
+    """the L2-resident schedule of sketch_sparse (spdata_gather_narrow_kernel: dc output rows per pass, operator slab of
+    dc x K floats, slabs generated on the auxiliary stream while the previous pass gathers), forced at small sizes with
+    RBX_SPD_DC: every format, both sides and layouts, both operator orientations and families, M not a multiple of dc,
+    alpha / beta, and bitwise reproducibility. The full-size C4 test takes this schedule by default."""
+    monkeypatch.setenv("RBX_SPD_DC", dc)
+    run_sparsedata_case(rb, cuda, "f64", "L", "C", "N", "N", 601, 300, 700, 1.5, -0.5, fmt, 0.05, off_s=(1, 2))
+    run_sparsedata_case(rb, cuda, "f32", "R", "R", "N", "N", 130, 400, 500, 1.0, 0.0, fmt, 0.1, fam="U")
+    run_sparsedata_case(rb, cuda, "f64", "L", "R", "T", "T", 64, 300, 700, 1.0, 2.0, fmt, 0.05, ma="S")
+    run_sparsedata_case(rb, cuda, "f64", "R", "C", "N", "N", 37, 90, 250, 2.0, 0.0, fmt, 0.3, fam="U", ma="S")
+    rng = np.random.default_rng(5)
+    A = to_fmt(rb, cuda, random_sparse(rng, 2000, 1500, 0.02, np.float64), fmt)
+    S = rb.DenseSkOp(rb.DenseDist(96, 2000), 3, dtype=torch.float64)
+    outs = []
+    for _ in range(3):
+        B = torch.zeros(96 * 1500, dtype=torch.float64, device=cuda)
+        rb.sketch_sparse(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 96, 1500, 2000, 1.0, S, 0, 0, A, 0, 0, 0.0, B, 96)
+        outs.append(B.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+    monkeypatch.delenv("RBX_SPD_DC", raising=False)
+
+
 @pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_general_sparse_operator_path_is_deterministic(rb, cuda, dt):
     """LASO, tall operators, explicit (filled) triplets and vec_nnz > 32 run the output-stationary gather of
