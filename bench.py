@@ -415,6 +415,17 @@ def main():
                "ms_steps": [round(t * 1e3, 1) for t in ts], "checksum0": chk, "host_memory": "pinned (torch pin_memory)"}
         # device path and host path agree
         assert torch.allclose(Bh, B.cpu(), rtol=1e-12, atol=1e-9)
+        if world == 1 and not args.no_extras:
+            # what a caller of the reference has: pageable memory (new T[]). The driver stages pageable copies through its own
+            # pinned bounce buffers, so the same call runs at a fraction of the link rate; reported beside the pinned figure.
+            Ap = torch.empty(m * n, dtype=torch.float64)
+            Ap.copy_(Ah)
+            Bp = torch.zeros(D * n, dtype=torch.float64)
+            tp = wall_time(torch, lambda: rb.sketch_general(rb.Layout(lay), rb.Op.NoTrans, rb.Op.NoTrans, D, n, m, 1.0, S, 0, 0, Ap, lda, 0.0, Bp, ldb), 1, warm=1)
+            e2e["pageable"] = {"value": flops(m, n) / tp / 1e9, "unit": "GFLOP/s", "ms_per_step": tp * 1e3,
+                               "note": "same call with pageable (unpinned) host buffers, as a caller's new T[] would be"}
+            assert torch.equal(Bp, Bh)
+            del Ap, Bp
 
     extras = {}
     if world == 1 and not args.no_extras:

@@ -3,6 +3,10 @@
 // dispatch to the sm_100a kernels. Nothing here computes sketches on the CPU.
 #include <atomic>
 #include <cmath>
+#include <cstring>
+#include <mutex>
+#include <thread>
+#include <vector>
 #include "rbx_kernels.cuh"
 
 namespace rbx {
@@ -311,6 +315,60 @@ static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_h
     return rc;
 }
 
+// ---- pageable host memory (what a caller's new T[] is) -----------------------------------------------------------------
+// cudaMemcpy from pageable memory goes through the driver's small bounce buffer at a fraction of the link rate (measured at
+// C2: 2.2 s per call against 0.32 s from pinned memory). The pipelined path below therefore stages pageable slabs itself:
+// several host threads copy the slab into one of two pinned bounce buffers (kept for the life of the process; released by
+// rbx_trim_workspace) while the previous slab crosses PCIe.
+struct PinnedBounce {
+    std::mutex mu;
+    void* buf[2] = { nullptr, nullptr };
+    size_t bytes = 0;
+    bool get(size_t need) {
+        if (need <= bytes && buf[0] && buf[1]) return true;
+        release();
+        for (int b = 0; b < 2; ++b)
+            if (cudaHostAlloc(&buf[b], need, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); release(); return false; }
+        bytes = need;
+        return true;
+    }
+    void release() {
+        for (int b = 0; b < 2; ++b) { if (buf[b]) cudaFreeHost(buf[b]); buf[b] = nullptr; }
+        bytes = 0;
+    }
+};
+static PinnedBounce& pinned_bounce() { static PinnedBounce p; return p; }
+
+static bool is_pageable(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return at.type == cudaMemoryTypeUnregistered;
+}
+// dst (packed: `runs` runs of run_bytes) <- src (runs `src_pitch` bytes apart), split over host threads
+static void parallel_gather_copy(uint8_t* dst, const uint8_t* src, size_t run_bytes, size_t runs, size_t src_pitch) {
+    unsigned nt = std::thread::hardware_concurrency();
+    if (nt > 16) nt = 16;
+    if (nt < 1) nt = 1;
+    const size_t total = run_bytes * runs;
+    if (total < ((size_t) 8 << 20)) nt = 1;
+    auto work = [=](unsigned t) {
+        // thread t takes bytes [t, t + 1) * total / nt of the packed destination
+        size_t b0 = total / nt * t, b1 = (t + 1 == nt) ? total : total / nt * (t + 1);
+        while (b0 < b1) {
+            const size_t run = b0 / run_bytes, off = b0 % run_bytes;
+            size_t n = run_bytes - off;
+            if (n > b1 - b0) n = b1 - b0;
+            std::memcpy(dst + b0, src + run * src_pitch + off, n);
+            b0 += n;
+        }
+    };
+    if (nt == 1) { work(0); return; }
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto& x : th) x.join();
+}
+
 // Left sketch of a large host matrix, pipelined: op(A) = A (K x N) is cut into row slabs along the contraction axis; slab
 // i+1 crosses PCIe while slab i is sketched with co_s advanced by the slab start and beta = 1 (the first slab carries the
 // caller's beta). Device memory: two slabs instead of all of A. body(k0, klen, A_slab, lda_slab, beta_eff, B_dev, stream).
@@ -330,6 +388,11 @@ static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, 
     cudaEvent_t copied[2] = { nullptr, nullptr }, consumed[2] = { nullptr, nullptr };
     int rc = RBX_OK;
     auto ok = [&](cudaError_t e) { if (e != cudaSuccess && rc == RBX_OK) { cudaGetLastError(); rc = RBX_ERR_CUDA; } return e == cudaSuccess; };
+    // pageable A: stage through our own pinned bounce buffers (see PinnedBounce); pinned / registered A goes straight to the copy engine
+    PinnedBounce& pb = pinned_bounce();
+    std::unique_lock<std::mutex> pb_lock(pb.mu, std::defer_lock);
+    bool bounce = is_pageable(A_host) && !getenv("RBX_NO_BOUNCE");
+    if (bounce) { pb_lock.lock(); bounce = pb.get((size_t) klen * N * sizeof(T)); if (!bounce) pb_lock.unlock(); }
     if (cudaMalloc(&slab[0], (size_t) klen * N * sizeof(T)) != cudaSuccess || cudaMalloc(&slab[1], (size_t) klen * N * sizeof(T)) != cudaSuccess ||
         cudaMalloc(&B_dev, nB * sizeof(T)) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
     if (rc == RBX_OK) {
@@ -342,7 +405,15 @@ static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, 
         const int64_t k0 = i * klen, kl = (k0 + klen < K) ? klen : K - k0;
         if (i >= 2) ok(cudaStreamWaitEvent(sc, consumed[b], 0));
         int64_t lda_slab;
-        if (layout == 'C') {        // K x N column-major: slab = kl contiguous elements of each of the N columns
+        if (bounce) {
+            // bounce buffer b was last read by the copy of slab i - 2: wait for that copy, pack the slab with host threads, then
+            // one contiguous copy (the host packs slab i + 1 while slab i crosses PCIe and slab i - 1 is sketched)
+            if (i >= 2) ok(cudaEventSynchronize(copied[b]));
+            uint8_t* dst = static_cast<uint8_t*>(pb.buf[b]);
+            if (layout == 'C') { lda_slab = kl; parallel_gather_copy(dst, reinterpret_cast<const uint8_t*>(A_host + k0), (size_t) kl * sizeof(T), (size_t) N, (size_t) lda * sizeof(T)); }
+            else               { lda_slab = N;  parallel_gather_copy(dst, reinterpret_cast<const uint8_t*>(A_host + k0 * lda), (size_t) N * sizeof(T), (size_t) kl, (size_t) lda * sizeof(T)); }
+            ok(cudaMemcpyAsync(slab[b], dst, (size_t) kl * N * sizeof(T), cudaMemcpyHostToDevice, sc));
+        } else if (layout == 'C') { // K x N column-major: slab = kl contiguous elements of each of the N columns
             lda_slab = kl;
             ok(cudaMemcpy2DAsync(slab[b], (size_t) kl * sizeof(T), A_host + k0, (size_t) lda * sizeof(T), (size_t) kl * sizeof(T), (size_t) N,
                                  cudaMemcpyHostToDevice, sc));
@@ -859,6 +930,7 @@ int rbx_stream_synchronize(void* stream) { return cudaStreamSynchronize((cudaStr
 int rbx_trim_workspace(void) {
     int dev = 0;
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetDevice(&dev) != cudaSuccess) return RBX_ERR_CUDA;
+    { PinnedBounce& pb = pinned_bounce(); std::lock_guard<std::mutex> g(pb.mu); pb.release(); }
     cudaMemPool_t pool = ws_pool(dev);
     if (!pool) return RBX_OK;
     return cudaMemPoolTrimTo(pool, 0) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;

@@ -66,6 +66,12 @@ constexpr uint32_t SASO_SIGN = 0x80000000u;
 #define SASO_NU_VAL 3
 #endif
 constexpr int SASO_NU = SASO_NU_VAL;          // codes held by a slot record; the rest of a slot's elements are its tail
+#ifndef SASO_PRED_ADD
+#define SASO_PRED_ADD 0   // 1: padded gathers carry their predicate to the add instead of zeroing the value register
+#endif
+#ifndef SASO_POLL_NS
+#define SASO_POLL_NS 0    // > 0: the producer warps sleep this many ns between polls of a stage's empty barrier
+#endif
 #ifndef SASO_GROUP
 #define SASO_GROUP 4      // slots whose records and gathers are in flight together
 #endif
@@ -298,6 +304,19 @@ template <> __device__ __forceinline__ uint32_t lds_raw_nz<float>(uint32_t addr,
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, %3;\n\tmov.b32 %0, 0;\n\t@p ld.shared.b32 %0, [%1];\n\t}" : "=r"(v) : "r"(addr), "r"(code), "r"(zero_code));
     return v;
 }
+// acc += (+/-) *(T*)addr unless code is the zero code: predicate, load, sign flip and add in one predicated sequence (no
+// zeroing of the value register; the predicate lives from the compare to the add). SASO_PRED_ADD selects it.
+template <typename T> __device__ __forceinline__ void lds_add_nz(T& acc, uint32_t addr, uint32_t code, uint32_t zero_code);
+template <> __device__ __forceinline__ void lds_add_nz<double>(double& acc, uint32_t addr, uint32_t code, uint32_t zero_code) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 lo, hi;\n\t.reg .f64 v;\n\tsetp.ne.u32 p, %2, %3;\n\t@p ld.shared.v2.b32 {lo, hi}, [%1];\n\t"
+                 "@p lop3.b32 hi, hi, %2, 0x80000000, 0x78;\n\t@p mov.b64 v, {lo, hi};\n\t@p add.f64 %0, %0, v;\n\t}"
+                 : "+d"(acc) : "r"(addr), "r"(code), "r"(zero_code));
+}
+template <> __device__ __forceinline__ void lds_add_nz<float>(float& acc, uint32_t addr, uint32_t code, uint32_t zero_code) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 x;\n\t.reg .f32 v;\n\tsetp.ne.u32 p, %2, %3;\n\t@p ld.shared.b32 x, [%1];\n\t"
+                 "@p lop3.b32 x, x, %2, 0x80000000, 0x78;\n\t@p mov.b32 v, x;\n\t@p add.f32 %0, %0, v;\n\t}"
+                 : "+f"(acc) : "r"(addr), "r"(code), "r"(zero_code));
+}
 __device__ __forceinline__ double apply_sign(unsigned long long bits, uint32_t code) {
     return __hiloint2double((int)((uint32_t)(bits >> 32) ^ (code & SASO_SIGN)), (int)(uint32_t) bits);
 }
@@ -338,6 +357,9 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, uint32
         for (int k = 0; k < SASO_NU; ++k)
 #pragma unroll
             for (int j = 0; j < G; ++j) {
+#if SASO_PRED_ADD
+                if (k >= SASO_ALWAYS) { lds_add_nz<T>(acc[g + j], lanebase + (c[j][k] << SH), c[j][k], zero_code); continue; }
+#endif
                 if (k < SASO_ALWAYS) {
                     if (sizeof(T) == 8) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(*reinterpret_cast<unsigned long long*>(&v[j][k])) : "r"(lanebase + (c[j][k] << SH)));
                     else asm volatile("ld.shared.b32 %0, [%1];" : "=r"(*reinterpret_cast<uint32_t*>(&v[j][k])) : "r"(lanebase + (c[j][k] << SH)));
@@ -346,7 +368,7 @@ __device__ __forceinline__ void saso_consume(T (&acc)[NS], uint32_t recs, uint32
                 }
             }
 #pragma unroll
-        for (int k = 0; k < SASO_NU; ++k)
+        for (int k = 0; k < (SASO_PRED_ADD ? SASO_ALWAYS : SASO_NU); ++k)
 #pragma unroll
             for (int j = 0; j < G; ++j) acc[g + j] += apply_sign(v[j][k], c[j][k]);
         uint32_t any = 0;
@@ -517,7 +539,13 @@ __global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const S
 #endif
         for (int ch = cb, it = 0; ch < ce; ch += cstep, ++it) {
             const int s = it % NST, u = it / NST;
-            if (u > 0) mbar_wait(&empty_bar[s], (uint32_t)(u - 1) & 1u);
+            if (u > 0) {
+#if SASO_POLL_NS > 0
+                while (!mbar_try_wait(&empty_bar[s], (uint32_t)(u - 1) & 1u)) __nanosleep(SASO_POLL_NS);
+#else
+                mbar_wait(&empty_bar[s], (uint32_t)(u - 1) & 1u);
+#endif
+            }
             load_async(ch, s);
             asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(smem_u32(&full_bar[s])) : "memory");
         }

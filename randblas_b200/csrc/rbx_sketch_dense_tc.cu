@@ -200,7 +200,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 const int e = gt + q * TC_GEN_WARPS * 32;
                 const int r = (int) crank * rows_per + (e >> 3), c = e & 7;
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (e < my_chunks && i0 + r < a.M && l0 + 4 * c < a.K) {
+                if (a.dbg & 48) {
+                    // pipe-conflict probe (tools/tc_time.py, RBX_TC_DBG 16 / 32): a dependent chain of 200 FP64 (16) or FP32 (32) FMAs
+                    // per operator chunk instead of the generator, to see which of them can run beside the tensor core
+                    if (a.dbg & 16) { double x = (double) e; for (int z = 0; z < 200; ++z) x = fma(x, 1.0000001, 1e-9); v.x = (float) x; }
+                    else { float x = (float) e; for (int z = 0; z < 200; ++z) x = fmaf(x, 1.0000001f, 1e-9f); v.x = x; }
+                } else if (e < my_chunks && i0 + r < a.M && l0 + 4 * c < a.K) {
                     if (FAMILY == 'X') {
                         v = __ldg(reinterpret_cast<const float4*>(a.Sx + (i0 + r) * a.s_pitch + l0 + 4 * c));
                     } else {
@@ -268,7 +273,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
                 xh[e] = hi; xl[e] = lo;
             }
-            fence_proxy_async();                           // generic-proxy writes -> visible to the tensor core (async proxy)
+            if (!(a.dbg & 64)) fence_proxy_async();        // generic-proxy writes -> visible to the tensor core (async proxy)
             __syncwarp();
             if (lane == 0) mbar_arrive(&ready_x[s]);
             if (FAMILY != 'X' && it + 1 < nit) generate(it + 1);

@@ -54,10 +54,22 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta)
                  "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
                  :: "r"(smem_u32(bar)), "r"(cta) : "memory");
 }
+// The suspend-time hint lets the hardware park the warp until the phase completes (or the hint elapses) instead of
+// returning at once: a waiting warp then costs a handful of issue slots per wait, not a spin loop's worth. (Measured on the
+// tcgen05 sketch: the TMA / MMA warps' polling alone filled 27 % of the issue slots and slowed the generator warps that
+// share their schedulers.) RBX_MBAR_HINT_NS = 0 restores the plain form.
+#ifndef RBX_MBAR_HINT_NS
+#define RBX_MBAR_HINT_NS 0        // measured: no gain on either kernel (try_wait already suspends the warp for a while)
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
+#if RBX_MBAR_HINT_NS > 0
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"((uint32_t) RBX_MBAR_HINT_NS) : "memory");
+#else
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+#endif
     return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) { while (!mbar_try_wait(bar, parity)) { } }
