@@ -16,9 +16,10 @@
 //    K-major operand layout, then the hi/lo split of the X tile in place; they are also the epilogue warps
 //    (tcgen05.ld -> alpha/beta -> global, or split-K partials summed in a fixed order by a second kernel).
 //  * the CTAs of one row block (same operator rows, different columns of X) form a thread-block cluster of up to 4:
-//    each generates 1/CL of the operator tile and writes it into every peer's shared memory with st.async (remote
-//    store that completes bytes on the peer's mbarrier), so a Gaussian sample is generated once per cluster;
-//  * mbarriers: full_x (TMA -> generators), ready_s (st.async bytes from all peers -> MMA), ready_x (generators ->
+//    each generates 1/CL of the operator tile into its own operand ring (plain vector stores) and a forwarder warp sends
+//    those rows to every peer with one bulk shared-to-shared copy per tile half (cp.async.bulk.shared::cluster, completes
+//    bytes on the peer's mbarrier), so a Gaussian sample is generated once per cluster;
+//  * mbarriers: full_x (TMA -> generators), gen_done (own rows stored -> MMA + forwarder), ready_s (bulk-copy bytes from the peers -> MMA), ready_x (generators ->
 //    MMA), empty (tcgen05.commit multicast to the whole cluster -> TMA + generators), done (last commit -> epilogue).
 // Envelope: implicit operator whose parent rows run along the contraction axis (l_on_cols), window column offset a
 // multiple of 4, X with unit stride along the contraction axis (e.g. ColMajor A in a left sketch), 16-byte aligned.
@@ -30,10 +31,13 @@
 namespace rbx {
 
 constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32;
+#ifndef TC_X_HI_RAW
+#define TC_X_HI_RAW 1
+#endif
 constexpr int TC_XST = 3;           // raw / hi X tiles in flight (hides the TMA latency)
 constexpr int TC_LST = 2;           // operator (hi + lo) tiles and X_lo tiles (produced on chip, one stage ahead is enough)
 constexpr int TC_EPI_WARPS = 16;     // generator warps that also run the epilogue (a multiple of 4)
-constexpr int TC_GEN_WARPS = 16, TC_THREADS = (2 + TC_GEN_WARPS) * 32;
+constexpr int TC_GEN_WARPS = 16, TC_THREADS = (3 + TC_GEN_WARPS) * 32;   // TMA, MMA, 16 generators, forwarder
 constexpr int TC_S_BYTES = TC_BM * TC_BK * 4;          // 16 KB: one of S_hi / S_lo
 constexpr int TC_X_BYTES = TC_BN * TC_BK * 4;          // 32 KB: one of X_hi / X_lo
 // shared-memory map: [X hi x3][X lo x2][S hi, S lo x2]
@@ -114,7 +118,7 @@ struct TcArgs {
 template <char FAMILY>
 __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t full_x[TC_XST], x_empty[TC_XST], ready_s[TC_LST], ready_x[TC_LST], l_empty[TC_LST], done;
+    __shared__ __align__(8) uint64_t full_x[TC_XST], x_empty[TC_XST], ready_s[TC_LST], ready_x[TC_LST], gen_done[TC_LST], l_empty[TC_LST], done;
     __shared__ uint32_t tmem_base_s;
     __shared__ double tab[32];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
@@ -130,7 +134,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
 
     if (tid == 0) {
         for (int s = 0; s < TC_XST; ++s) { mbar_init(&full_x[s], 1); mbar_init(&x_empty[s], 1); }
-        for (int s = 0; s < TC_LST; ++s) { mbar_init(&ready_s[s], 1); mbar_init(&ready_x[s], TC_GEN_WARPS); mbar_init(&l_empty[s], (uint32_t) a.cl); }
+        for (int s = 0; s < TC_LST; ++s) { mbar_init(&ready_s[s], 1); mbar_init(&ready_x[s], TC_GEN_WARPS); mbar_init(&gen_done[s], TC_GEN_WARPS); mbar_init(&l_empty[s], (uint32_t) a.cl); }
         mbar_init(&done, 1);
         fence_mbar_init();
         tma_prefetch_desc(&tmap_x);
@@ -161,7 +165,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
             constexpr uint32_t idesc = tc_idesc(TC_BN);
             for (int it = 0; it < nit; ++it) {
                 const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
-                mbar_wait(&ready_s[s], u & 1);
+                mbar_wait(&gen_done[s], u & 1);            // this CTA's rows of the operator tile (generic stores + proxy fence)
+                mbar_wait(&ready_s[s], u & 1);             // the peers' rows (bulk copies into this CTA)
                 mbar_wait(&ready_x[s], u & 1);
                 fence_proxy_async();                       // st.async / generic writes -> tensor-core (async proxy) reads
                 tc_fence_after();
@@ -181,6 +186,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 if (a.cl > 1) umma_commit_mcast(&l_empty[s], (uint16_t)((1u << a.cl) - 1u)); else umma_commit(&l_empty[s]);
             }
             umma_commit(&done);
+        }
+    } else if (warp == 2 + TC_GEN_WARPS) {
+        // ---- forwarder: when this CTA's rows of a stage are in its own shared memory, one bulk copy per peer and half (hi / lo)
+        // carries them into the peers' operand rings and completes the bytes on their ready_s barriers. (Round 1 handed every
+        // 16-byte chunk over with its own st.async; those small async-proxy writes did not overlap with the tensor core's operand
+        // reads: a probe with the stores on cost 0.76 ms beside the MMAs, 0.50 ms with them off.)
+        if (lane == 0 && a.cl > 1) {
+            const uint32_t part = (uint32_t)(TC_BM / a.cl) * 128u;      // bytes of this CTA's rows in one of the hi / lo tiles
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % TC_LST, u = it / TC_LST;
+                mbar_wait(&gen_done[s], u & 1);
+                const uint32_t src = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES + crank * part, bar_u32 = smem_u32(&ready_s[s]);
+                for (uint32_t p = 0; p < (uint32_t) a.cl; ++p) {
+                    if (p == crank) continue;
+                    const uint32_t dst = mapa_u32(src, p), bar = mapa_u32(bar_u32, p);
+                    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 :: "r"(dst), "r"(src), "r"(part), "r"(bar) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 :: "r"(dst + TC_S_BYTES), "r"(src + TC_S_BYTES), "r"(part), "r"(bar) : "memory");
+                }
+            }
         }
     } else {
         // ---- generators / converters ----
@@ -226,8 +252,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
         for (int it = 0; it < nit; ++it) {
             const int s = it % TC_LST, u = it / TC_LST, xs = it % TC_XST;
             if (u > 0) mbar_wait(&l_empty[s], (u - 1) & 1);
-            if (gt == 0) mbar_expect_tx(&ready_s[s], 2 * TC_S_BYTES);      // hi + lo tiles, written by the whole cluster
-            const uint32_t st_u32 = smem0 + TC_OFF_S + (uint32_t) s * 2 * TC_S_BYTES, bar_u32 = smem_u32(&ready_s[s]);
+            if (gt == 0) mbar_expect_tx(&ready_s[s], (uint32_t)(2 * TC_S_BYTES / a.cl * (a.cl - 1)));      // the peers' rows of the hi + lo tiles
+            uint8_t* st_loc = smem + TC_OFF_S + (size_t) s * 2 * TC_S_BYTES;
+            const uint32_t bar_u32 = smem_u32(&ready_s[s]);
 #pragma unroll
             for (int q = 0; q < NCH; ++q) {
                 const int e = gt + q * TC_GEN_WARPS * 32;
@@ -246,17 +273,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                     hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
                     hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
                     const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
-                    for (int p = 0; p < a.cl; ++p) {
-                        const uint32_t dst = mapa_u32(st_u32 + off, (uint32_t) p), bar = mapa_u32(bar_u32, (uint32_t) p);
-                        st_async_v4(dst, hi, bar);
-                        st_async_v4(dst + TC_S_BYTES, lo, bar);
-                    }
+                    *reinterpret_cast<float4*>(st_loc + off) = hi;                        // this CTA's own ring; the forwarder copies the
+                    *reinterpret_cast<float4*>(st_loc + TC_S_BYTES + off) = lo;           // rows to the peers in bulk
                 }
             }
-            if ((a.dbg & 1) && gt == 0) {                  // debug: nothing generated, complete the bytes by hand
-                for (int p = 0; p < a.cl; ++p)
-                    asm volatile("mbarrier.complete_tx.relaxed.cluster.shared::cluster.b64 [%0], %1;" :: "r"(mapa_u32(bar_u32, (uint32_t) p)), "r"(2 * TC_S_BYTES / a.cl) : "memory");
-            }
+            fence_proxy_async();                           // generic stores -> visible to the tensor core and to the bulk-copy engine
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&gen_done[s]);
             // operator values read from memory: issue the loads of the next stage now, so that their latency is covered by
             // the X split below (the generated families compute theirs after handing the stage over instead)
             if (FAMILY == 'X' && it + 1 < nit) generate(it + 1);
@@ -271,7 +294,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
                 hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
                 hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
                 hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
+#if TC_X_HI_RAW
+                xl[e] = lo;          // the raw tile serves as X_hi: kind::tf32 reads the top 19 bits of each operand word and ignores the rest
+#else
                 xh[e] = hi; xl[e] = lo;
+#endif
             }
             if (!(a.dbg & 64)) fence_proxy_async();        // generic-proxy writes -> visible to the tensor core (async proxy)
             __syncwarp();
