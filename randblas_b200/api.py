@@ -367,6 +367,15 @@ def _sketch(side, layout, opS, opA, p0, p1, p2, alpha, S, ro_s, co_s, A, lda, be
             _call(f"rbx_sketch_dense_{suf}", *head, *op, _ptr(S.buff), _c(S.layout), *tail, _stream(B))
     elif isinstance(S, SparseSkOp):
         D = S.dist
+        if S.known_filled and host:
+            # explicit (possibly caller-edited) triplets with host data: stage A and B and take the same COO path as device data
+            dev = S.vals.device
+            rowsA = (p2 if Op(opA) == Op.NoTrans else p1) if side == "L" else (p0 if Op(opA) == Op.NoTrans else p2)
+            Ad = A.to(dev, non_blocking=True)
+            Bd = B.to(dev, non_blocking=True)
+            _sketch(side, layout, opS, opA, p0, p1, p2, alpha, S, ro_s, co_s, Ad, lda, beta, Bd, ldb)
+            B.copy_(Bd)
+            return
         if S.known_filled and not host:
             # explicit triplets (possibly modified by the caller): left_spmm / right_spmm on the COO view
             r64, c64 = S.rows.to(torch.int64), S.cols.to(torch.int64)
@@ -474,6 +483,10 @@ def sketch_sparse(layout, op1, op2, p0, p1, p2, alpha, *rest):
         A, ro_a, co_a, S, ro_s, co_s, beta, B, ldb = rest
     D = S.dist
     dt = B.dtype
+    if S.buff is not None or D.family == DenseDistName.BlackBox:
+        # the reference multiplies by S.buff here (sksp.hh:166-172); the device path regenerates the operator from its seed,
+        # which an explicit buffer may not match
+        raise Error("sketch_sparse takes an implicit DenseSkOp (S.buff is None) on the device; use sketch_general on A^T for an explicit operator")
     if not B.is_cuda:
         # host arrays (what a caller of the reference owns): stage the sparse matrix and B through HBM around the device call
         dev = torch.device("cuda", torch.cuda.current_device())

@@ -74,6 +74,11 @@ int launch_fisher_yates(const Ctr128& ctr, const Key64& key, int64_t vec_nnz, in
         return check_launch("fisher_yates_lazy_kernel");
     }
     int64_t ctas = dim_minor < kNumSMs * 4 ? dim_minor : kNumSMs * 4;
+    // one work array of (dim_major + vec_nnz) int64 per CTA: the CTA count follows the memory that is free (at most 1 GiB)
+    const size_t per_cta = sizeof(int64_t) * (size_t)(dim_major + vec_nnz);
+    const int64_t fit = (int64_t)(ws_budget((size_t) 1 << 30) / per_cta);
+    if (fit < 1) return RBX_ERR_ALLOC;
+    if (ctas > fit) ctas = fit;
     int64_t* scratch = nullptr;
     if (ws_alloc(&scratch, sizeof(int64_t) * (size_t)(ctas * (dim_major + vec_nnz)), stream) != cudaSuccess) {
         cudaGetLastError();

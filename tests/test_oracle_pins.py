@@ -105,6 +105,25 @@ def test_oracle_vs_compiled_reference_random():
         assert a[4] == b[4]
 
 
+def test_uniform_transforms_documented_properties():
+    """Random123's u01 / uneg11 (uniform.hpp) are restated in oracle/shims (no checkout offline). Their documented contract
+    pins the restatement at the edges: u01<float> maps into (0, 1] -- never 0, exactly 1 at the top word -- and is
+    monotone; uneg11<float> maps into [-1, 1], never 0, antisymmetric about the half-way word up to the 2^-32 offset."""
+    u01, un = ol.ORC.orc_u01, ol.ORC.orc_uneg11
+    assert u01(0) == 2.0 ** -33 and u01(0xFFFFFFFF) == 1.0 and u01(0x80000000) == 0.5
+    assert un(0) == 2.0 ** -32 and un(0x7FFFFFFF) == 1.0 and un(0x80000000) == -1.0 and un(0xFFFFFFFF) == np.float32(-2.0 ** -31 + 2.0 ** -32)
+    words = np.array([0, 1, 2, 255, 256, 0x7FFFFF, 0x800000, 0x1000000, 0x7FFFFFFF, 0x80000000, 0x80000001, 0xFFFFFF00, 0xFFFFFFFF], np.uint64)
+    vals = [u01(int(w)) for w in words]
+    assert all(0.0 < v <= 1.0 for v in vals) and all(a <= b for a, b in zip(vals, vals[1:]))
+    assert all(-1.0 <= un(int(w)) <= 1.0 and un(int(w)) != 0.0 for w in words)
+    # the compiled reference (through the shims) produces the same floats lane by lane
+    if ol.REF is not None:
+        for ctr in ([0, 0, 0, 0], [5, 0, 0, 7]):
+            raw = ol.philox(ctr, [3, 0], "ref")
+            got = ol.generate4("U", ctr, [3, 0], "ref")
+            assert [float(g) for g in got] == [un(w) for w in raw]
+
+
 def test_libm_models_match_host_libm_strided():
     """oracle's explicit-FMA models == this host's sincosf/logf on a 2^22-point strided sweep of the 2^32 domain
     (the full sweep, run once by hand, is recorded in DESIGN.md: 0 mismatches on glibc 2.39 / FMA)."""
