@@ -472,6 +472,38 @@ def sketch_symmetric(layout, *rest, sym_check_tol=0):
     return sketch_general(layout, Op.NoTrans, Op.NoTrans, n, d, n, alpha, A, lda, S, ro_s, co_s, beta, B, ldb)
 
 
+def _coo_triplets(A):
+    """(rows, cols, vals) of a COO / CSR / CSC container as int64 device arrays (rbx_expand_ptr expands a pointer array)"""
+    i0, i1 = A._idx()
+    if A.fmt == "O":
+        return i0, i1, A.vals
+    outer = torch.empty(max(A.nnz, 1), dtype=torch.int64, device=A.vals.device)
+    n_outer = A.n_rows if A.fmt == "R" else A.n_cols
+    _call("rbx_expand_ptr", n_outer, _ptr(i0 if A.fmt == "R" else i1), _ptr(outer), _stream(A.vals))
+    return (outer[: A.nnz], i1, A.vals) if A.fmt == "R" else (i0, outer[: A.nnz], A.vals)
+
+
+def left_spmm(layout, opA, opB, d, n, m, alpha, A, ro_a, co_a, B, ldb, beta, C, ldc):
+    """sparse_data::left_spmm (spmm_dispatch.hh:48-160): C (d x n) = alpha * op(submat(A)) (d x m, sparse) * op(B) (m x n) + beta * C
+    for a COOMatrix / CSRMatrix / CSCMatrix A on the device. Output-stationary gather, no atomics (rbx_spmm_coo_*)."""
+    if A.fmt != "O" and (ro_a != 0 or co_a != 0):
+        raise Error("CSR / CSC operands are taken whole (spmm_dispatch.hh:97-104)")
+    rows, cols, vals = _coo_triplets(A)
+    dt = C.dtype
+    _call(f"rbx_spmm_coo_{_suf(dt)}", b"L", _c(layout), _c(opA), _c(opB), d, n, m, _scalar(dt, alpha), A.n_rows, A.n_cols, A.nnz,
+          _ptr(rows), _ptr(cols), _ptr(vals), ro_a, co_a, _ptr(B), ldb, _scalar(dt, beta), _ptr(C), ldc, _stream(C))
+    if A.fmt != "O":
+        torch.cuda.current_stream(C.device).synchronize()      # the expanded index array is released on return
+
+
+def right_spmm(layout, opA, opB, m, d, n, alpha, A, lda, B, ro_b, co_b, beta, C, ldc):
+    """sparse_data::right_spmm (spmm_dispatch.hh:162-200): C (m x d) = alpha * op(A) (m x n, dense) * op(submat(B)) (n x d, sparse)
+    + beta * C, as the transposed left product in the opposite layout."""
+    t_opB = Op.Trans if Op(opB) == Op.NoTrans else Op.NoTrans
+    t_layout = Layout.RowMajor if Layout(layout) == Layout.ColMajor else Layout.ColMajor
+    left_spmm(t_layout, t_opB, opA, d, m, n, alpha, B, ro_b, co_b, A, lda, beta, C, ldc)
+
+
 def sketch_sparse(layout, op1, op2, p0, p1, p2, alpha, *rest):
     """sksp.hh:464-485 (left: layout, opS, opA, d, n, m, alpha, S, ro_s, co_s, A, ro_a, co_a, beta, B, ldb) and
     sksp.hh:595-616 (right: layout, opA, opS, m, d, n, alpha, A, ro_a, co_a, S, ro_s, co_s, beta, B, ldb)."""

@@ -332,6 +332,44 @@ def test_sketch_sparse_row_blocked_passes(rb, cuda, fmt, dc, monkeypatch):
     monkeypatch.delenv("RBX_SPD_DC", raising=False)
 
 
+@pytest.mark.parametrize("fmt", ["O", "R", "C"])
+def test_left_and_right_spmm_public_entry_points(rb, cuda, fmt):
+    """sparse_data::left_spmm / right_spmm (spmm_dispatch.hh:48-200; test_spmm_{coo,csr,csc}.cc) on device containers: both
+    layouts, transposes of either operand, alpha / beta, sub-matrix offsets (COO), against a dense product"""
+    rng = np.random.default_rng(21)
+    d, n, m = 23, 17, 140
+    for layout in "CR":
+        for opA in "NT":
+            for opB in "NT":
+                Am = random_sparse(rng, *((d, m) if opA == "N" else (m, d)), 0.15, np.float64)
+                Bm = rng.standard_normal((m, n) if opB == "N" else (n, m))
+                C0 = rng.standard_normal((d, n))
+                A = to_fmt(rb, cuda, Am, fmt)
+                ldb = Bm.shape[0] if layout == "C" else Bm.shape[1]
+                ldc = d if layout == "C" else n
+                Bf = torch.from_numpy(np.ascontiguousarray(Bm.T if layout == "C" else Bm).ravel()).to(cuda)
+                Cf = torch.from_numpy(np.ascontiguousarray(C0.T if layout == "C" else C0).ravel()).to(cuda)
+                rb.left_spmm(rb.Layout(layout), rb.Op(opA), rb.Op(opB), d, n, m, 1.5, A, 0, 0, Bf, ldb, -0.5, Cf, ldc)
+                want = 1.5 * (Am if opA == "N" else Am.T) @ (Bm if opB == "N" else Bm.T) - 0.5 * C0
+                got = Cf.cpu().numpy().reshape((n, d)).T if layout == "C" else Cf.cpu().numpy().reshape((d, n))
+                assert np.allclose(got, want, rtol=1e-12, atol=1e-12), (fmt, layout, opA, opB)
+    # right_spmm: C (m x d) = A (m x n dense) * B (n x d sparse)
+    mm, dd, nn = 19, 11, 90
+    Bs = random_sparse(rng, nn, dd, 0.2, np.float64)
+    Ad = rng.standard_normal((mm, nn))
+    C = torch.zeros(mm * dd, dtype=torch.float64, device=cuda)
+    rb.right_spmm(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, mm, dd, nn, 1.0, torch.from_numpy(np.ascontiguousarray(Ad.T).ravel()).to(cuda), mm,
+                  to_fmt(rb, cuda, Bs, fmt), 0, 0, 0.0, C, mm)
+    assert np.allclose(C.cpu().numpy().reshape(dd, mm).T, Ad @ Bs, rtol=1e-12, atol=1e-12)
+    if fmt == "O":        # sub-matrix of a COO operand
+        Big = random_sparse(rng, 40, 160, 0.2, np.float64)
+        A = to_fmt(rb, cuda, Big, "O")
+        Bm = rng.standard_normal((m, n))
+        Cf = torch.zeros(d * n, dtype=torch.float64, device=cuda)
+        rb.left_spmm(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, A, 5, 9, torch.from_numpy(np.ascontiguousarray(Bm.T).ravel()).to(cuda), m, 0.0, Cf, d)
+        assert np.allclose(Cf.cpu().numpy().reshape(n, d).T, Big[5:5 + d, 9:9 + m] @ Bm, rtol=1e-12, atol=1e-12)
+
+
 @pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_general_sparse_operator_path_is_deterministic(rb, cuda, dt):
     """LASO, tall operators, explicit (filled) triplets and vec_nnz > 32 run the output-stationary gather of
