@@ -86,15 +86,40 @@ static int fill_dense(char layout, int64_t D_rows, int64_t D_cols, char family, 
 template <typename T>
 static int host_fill_dense(char layout, int64_t D_rows, int64_t D_cols, char family, char major_axis, int64_t n_rows, int64_t n_cols,
                            int64_t ro_s, int64_t co_s, T* buff_host, const uint32_t* ctr, const uint32_t* key, uint32_t* next_ctr) {
-    { DryRun dry; RBX_TRY(fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, (T*) nullptr, ctr, key, nullptr, nullptr)); }
+    // argument checks and the returned state, without touching the device
+    { DryRun dry; RBX_TRY(fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, (T*) nullptr, ctr, key, next_ctr, nullptr)); }
     RBX_NEED_DEVICE();
-    const size_t bytes = sizeof(T) * (size_t) n_rows * (size_t) n_cols;
-    T* dev = nullptr;
-    if (bytes == 0) return fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, dev, ctr, key, next_ctr, nullptr);
-    if (cudaMalloc(&dev, bytes) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
-    int rc = fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, n_cols, ro_s, co_s, dev, ctr, key, next_ctr, nullptr);
-    if (rc == RBX_OK && cudaMemcpy(buff_host, dev, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) rc = RBX_ERR_CUDA;
-    cudaFree(dev);
+    if (n_rows == 0 || n_cols == 0) return RBX_OK;
+    // The window is generated in chunks of its slow axis (about 256 MB each) on two streams: chunk i + 1 is generated while
+    // chunk i crosses PCIe, and the device holds two chunks instead of the whole window (17 GB at C3).
+    const int64_t fast = (layout == 'C') ? n_rows : n_cols, slow = (layout == 'C') ? n_cols : n_rows;
+    int64_t per = ((int64_t) 256 << 20) / (fast * (int64_t) sizeof(T));
+    if (per < 1) per = 1;
+    if (per > slow) per = slow;
+    const size_t chunk_bytes = (size_t) per * fast * sizeof(T);
+    T* buf[2] = { nullptr, nullptr };
+    cudaStream_t st[2] = { nullptr, nullptr };
+    int rc = RBX_OK;
+    const int nbuf = per < slow ? 2 : 1;
+    for (int b = 0; b < nbuf && rc == RBX_OK; ++b) {
+        if (ws_alloc(&buf[b], chunk_bytes, nullptr) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
+        else if (cudaStreamCreateWithFlags(&st[b], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    }
+    if (rc == RBX_OK && cudaStreamSynchronize(nullptr) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }
+    int64_t i = 0;
+    for (int64_t s0 = 0; s0 < slow && rc == RBX_OK; s0 += per, ++i) {
+        const int b = (int)(i % nbuf);
+        const int64_t len = (slow - s0 < per) ? slow - s0 : per;
+        if (layout == 'C') rc = fill_dense<T>(layout, D_rows, D_cols, family, major_axis, n_rows, len, ro_s, co_s + s0, buf[b], ctr, key, nullptr, (void*) st[b]);
+        else               rc = fill_dense<T>(layout, D_rows, D_cols, family, major_axis, len, n_cols, ro_s + s0, co_s, buf[b], ctr, key, nullptr, (void*) st[b]);
+        if (rc == RBX_OK && cudaMemcpyAsync(buff_host + s0 * fast, buf[b], (size_t) len * fast * sizeof(T), cudaMemcpyDeviceToHost, st[b]) != cudaSuccess) {
+            cudaGetLastError(); rc = RBX_ERR_CUDA;
+        }
+    }
+    for (int b = 0; b < nbuf; ++b) {
+        if (st[b]) { if (cudaStreamSynchronize(st[b]) != cudaSuccess && rc == RBX_OK) { cudaGetLastError(); rc = RBX_ERR_CUDA; } cudaStreamDestroy(st[b]); }
+        if (buf[b]) cudaFreeAsync(buf[b], nullptr);
+    }
     return rc;
 }
 
@@ -303,15 +328,18 @@ static int with_staged(char layout, int64_t rows_A, int64_t cols_A, const T* A_h
     T *A_dev = nullptr, *B_dev = nullptr;
     cudaStream_t st = nullptr;
     int rc = RBX_OK;
-    if ((nA && cudaMalloc(&A_dev, nA * sizeof(T)) != cudaSuccess) || (nB && cudaMalloc(&B_dev, nB * sizeof(T)) != cudaSuccess)) {
+    // staging buffers come from the library's stream-ordered pool: a repeated call reuses the mapping of the previous one
+    // instead of paying cudaMalloc / cudaFree (milliseconds for a few hundred MB) every time
+    if ((nA && ws_alloc(&A_dev, nA * sizeof(T), st) != cudaSuccess) || (nB && ws_alloc(&B_dev, nB * sizeof(T), st) != cudaSuccess)) {
         cudaGetLastError(); rc = RBX_ERR_ALLOC;
     }
     if (rc == RBX_OK && nA && cudaMemcpyAsync(A_dev, A_host, nA * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
     if (rc == RBX_OK && nB && read_B && cudaMemcpyAsync(B_dev, B_host, nB * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
     if (rc == RBX_OK) rc = body(A_dev, B_dev, (void*) st);
     if (rc == RBX_OK && copy_back_view<T>(B_host, B_dev, vb, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (A_dev) cudaFreeAsync(A_dev, st);
+    if (B_dev) cudaFreeAsync(B_dev, st);
     if (cudaStreamSynchronize(st) != cudaSuccess && rc == RBX_OK) rc = RBX_ERR_CUDA;
-    cudaFree(A_dev); cudaFree(B_dev);
     return rc;
 }
 
@@ -393,8 +421,9 @@ static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, 
     std::unique_lock<std::mutex> pb_lock(pb.mu, std::defer_lock);
     bool bounce = is_pageable(A_host) && !getenv("RBX_NO_BOUNCE");
     if (bounce) { pb_lock.lock(); bounce = pb.get((size_t) klen * N * sizeof(T)); if (!bounce) pb_lock.unlock(); }
-    if (cudaMalloc(&slab[0], (size_t) klen * N * sizeof(T)) != cudaSuccess || cudaMalloc(&slab[1], (size_t) klen * N * sizeof(T)) != cudaSuccess ||
-        cudaMalloc(&B_dev, nB * sizeof(T)) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
+    if (ws_alloc(&slab[0], (size_t) klen * N * sizeof(T), nullptr) != cudaSuccess || ws_alloc(&slab[1], (size_t) klen * N * sizeof(T), nullptr) != cudaSuccess ||
+        ws_alloc(&B_dev, nB * sizeof(T), nullptr) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_ALLOC; }
+    if (rc == RBX_OK && cudaStreamSynchronize(nullptr) != cudaSuccess) { cudaGetLastError(); rc = RBX_ERR_CUDA; }   // the buffers are used on other streams
     if (rc == RBX_OK) {
         ok(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking)); ok(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
         for (int b = 0; b < 2; ++b) { ok(cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming)); ok(cudaEventCreateWithFlags(&consumed[b], cudaEventDisableTiming)); }
@@ -433,7 +462,7 @@ static int staged_left_slabs(char layout, int64_t rows_B, int64_t N, int64_t K, 
     for (int b = 0; b < 2; ++b) { if (copied[b]) cudaEventDestroy(copied[b]); if (consumed[b]) cudaEventDestroy(consumed[b]); }
     if (sc) cudaStreamDestroy(sc);
     if (sx) cudaStreamDestroy(sx);
-    cudaFree(slab[0]); cudaFree(slab[1]); cudaFree(B_dev);
+    for (T* q : { slab[0], slab[1], B_dev }) if (q) cudaFreeAsync(q, nullptr);       // both work streams were synchronised above
     return rc;
 }
 // the pipelined path applies to plain left sketches of a host matrix of at least 1 GiB
