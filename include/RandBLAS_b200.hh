@@ -417,6 +417,9 @@ template <typename T> struct fn {
     static host_sketch_sparseop_t host_sketch_sparseop() { return (host_sketch_sparseop_t) RBX_PICK(T, rbx_host_sketch_sparseop); }
     static spmm_coo_t spmm_coo() { return (spmm_coo_t) RBX_PICK(T, rbx_spmm_coo); }
     static sparsedata_t sparsedata() { return (sparsedata_t) RBX_PICK(T, rbx_sketch_sparsedata); }
+    using host_sparsedata_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
+                                      int64_t, int64_t, char, int64_t, int64_t, int64_t, const T*, const int64_t*, const int64_t*, int64_t, int64_t, T, T*, int64_t);
+    static host_sparsedata_t host_sparsedata() { return (host_sparsedata_t) RBX_PICK(T, rbx_host_sketch_sparsedata); }
 };
 #undef RBX_PICK
 }  // namespace detail
@@ -741,17 +744,11 @@ inline void sksp3(char side, blas::Layout layout, blas::Op opS, blas::Op opA, in
         }
         return;
     }
-    const int64_t rB = p0, cB = p1;
-    randblas_require(ldb >= (layout == blas::Layout::ColMajor ? rB : cB));
-    const uint64_t nB = span(layout, rB, cB, ldb);
+    // host arrays: the library stages the matrix and B (rbx_host_sketch_sparsedata_*); 32-bit indices are widened first
     const std::vector<int64_t> a0 = widen(i0, n0), a1 = widen(i1, n1);
-    DevBuf d0(a0.data(), n0 * 8), d1(a1.data(), n1 * 8), dv(A.vals, A.nnz * sizeof(T)),
-           dB((beta != (T) 0 || padded(layout, rB, cB, ldb)) ? B : nullptr, nB * sizeof(T));
-    check(fn<T>::sparsedata()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
-                              S.seed_state.counter.v, S.seed_state.key.v, ro_s, co_s, fmt, A.n_rows, A.n_cols, A.nnz, (const T*) dv.p,
-                              (const int64_t*) d0.p, (const int64_t*) d1.p, ro_a, co_a, beta, (T*) dB.p, ldb, nullptr), "sketch_sparse");
-    check(rbx_memcpy_d2h(B, dB.p, nB * sizeof(T), nullptr), "rbx_memcpy_d2h");
-    check(rbx_stream_synchronize(nullptr), "rbx_stream_synchronize");
+    check(fn<T>::host_sparsedata()(side, ch(layout), ch(opS), ch(opA), p0, p1, p2, alpha, D.n_rows, D.n_cols, (char) D.family, (char) D.major_axis,
+                                   S.seed_state.counter.v, S.seed_state.key.v, ro_s, co_s, fmt, A.n_rows, A.n_cols, A.nnz, A.vals,
+                                   a0.data(), a1.data(), ro_a, co_a, beta, B, ldb), "sketch_sparse");
 }
 }  // namespace detail
 

@@ -229,6 +229,19 @@ int rbx_sketch_sparsedata_f64(char side, char layout, char opS, char opA, int64_
                               const double* vals_dev, const int64_t* idx0_dev, const int64_t* idx1_dev, int64_t ro_a, int64_t co_a,
                               double beta, double* B_dev, int64_t ldb, void* stream);
 
+/* the same with every array in host memory (the arrays a caller of RandBLAS::sketch_sparse owns, sksp.hh:464-616): the sparse
+ * matrix and B are staged through device memory around the call; synchronous */
+int rbx_host_sketch_sparsedata_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                                   int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                   int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, int64_t nnz,
+                                   const float* vals_host, const int64_t* idx0_host, const int64_t* idx1_host, int64_t ro_a, int64_t co_a,
+                                   float beta, float* B_host, int64_t ldb);
+int rbx_host_sketch_sparsedata_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                                   int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
+                                   int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, int64_t nnz,
+                                   const double* vals_host, const int64_t* idx0_host, const int64_t* idx1_host, int64_t ro_a, int64_t co_a,
+                                   double beta, double* B_host, int64_t ldb);
+
 /* ---- multi-GPU (reference contract: rtd/source/tutorial/updates.rst:59-80, skge.hh:182-189) ----------------------
  * One process per GPU. rbx_shard_range: rank's [start, start+len) of `total`, in units of `align`.
  * Column-sharded sketches need no entry point: every rank calls rbx_sketch_* on its own column slab with the same operator.

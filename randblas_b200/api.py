@@ -520,17 +520,13 @@ def sketch_sparse(layout, op1, op2, p0, p1, p2, alpha, *rest):
         # which an explicit buffer may not match
         raise Error("sketch_sparse takes an implicit DenseSkOp (S.buff is None) on the device; use sketch_general on A^T for an explicit operator")
     if not B.is_cuda:
-        # host arrays (what a caller of the reference owns): stage the sparse matrix and B through HBM around the device call
-        dev = torch.device("cuda", torch.cuda.current_device())
+        # host arrays (what a caller of the reference owns): rbx_host_sketch_sparsedata_* stages the sparse matrix and B
+        # through HBM around the device call
         i0, i1 = A._idx()
-        Ad = type(A)(A.n_rows, A.n_cols, A.vals.to(dev, non_blocking=True), i0.to(dev, non_blocking=True), i1.to(dev, non_blocking=True))
-        rows_B, cols_B = p0, p1
-        inner, outer = (rows_B, cols_B) if Layout(layout) == Layout.ColMajor else (cols_B, rows_B)
-        keep = beta != 0 or (ldb > inner and outer > 1)          # B as a window of a larger array: its padding must survive
-        Bd = B.to(dev, non_blocking=True) if keep else torch.empty(B.numel(), dtype=dt, device=dev)
-        rest = (S, ro_s, co_s, Ad, ro_a, co_a, beta, Bd, ldb) if side == "L" else (Ad, ro_a, co_a, S, ro_s, co_s, beta, Bd, ldb)
-        sketch_sparse(layout, op1, op2, p0, p1, p2, alpha, *rest)
-        B.copy_(Bd)
+        _call(f"rbx_host_sketch_sparsedata_{_suf(dt)}", _c(side), _c(layout), _c(opS), _c(opA), p0, p1, p2, _scalar(dt, alpha),
+              D.n_rows, D.n_cols, _c(D.family), _c(D.major_axis), _u32(S.seed_state.counter), _u32(S.seed_state.key),
+              ro_s, co_s, A.fmt.encode(), A.n_rows, A.n_cols, A.nnz, _ptr(A.vals), _ptr(i0), _ptr(i1), ro_a, co_a,
+              _scalar(dt, beta), _ptr(B), ldb)
         return
     i0, i1 = A._idx()
     _call(f"rbx_sketch_sparsedata_{_suf(dt)}", _c(side), _c(layout), _c(opS), _c(opA), p0, p1, p2, _scalar(dt, alpha),

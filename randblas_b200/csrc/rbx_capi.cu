@@ -667,6 +667,44 @@ static int sketch_sparsedata(char side, char layout, char opS, char opA, int64_t
     return rc;
 }
 
+// sketch_sparse with every array in host memory (what a caller of the reference owns): the sparse matrix (vals and both index
+// arrays) and B are staged through the library's stream-ordered pool around the device call; B comes back view-only when it
+// is a window of a larger array. Argument errors are reported before the device is touched.
+template <typename T>
+static int host_sketch_sparsedata(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                                  int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t* ctr, const uint32_t* key,
+                                  int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, int64_t nnz,
+                                  const T* vals_h, const int64_t* idx0_h, const int64_t* idx1_h, int64_t ro_a, int64_t co_a,
+                                  T beta, T* B_host, int64_t ldb) {
+    { DryRun dry; RBX_TRY(sketch_sparsedata<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s,
+                                               fmt, A_rows, A_cols, nnz, (const T*) nullptr, (const int64_t*) nullptr, (const int64_t*) nullptr,
+                                               ro_a, co_a, beta, (T*) nullptr, ldb, nullptr)); }
+    RBX_NEED_DEVICE();
+    const HostView vb = host_view<T>(layout, p0, p1, ldb);              // B is p0 x p1 on both sides (d x n left, m x d right)
+    const bool read_B = beta != (T) 0 || vb.need_upload;
+    const size_t n0 = (size_t)(fmt == 'R' ? A_rows + 1 : nnz), n1 = (size_t)(fmt == 'C' ? A_cols + 1 : nnz);
+    T *vals = nullptr, *B_dev = nullptr; int64_t *i0 = nullptr, *i1 = nullptr;
+    cudaStream_t st = nullptr;
+    int rc = RBX_OK;
+    if ((nnz && ws_alloc(&vals, (size_t) nnz * sizeof(T), st) != cudaSuccess) || (n0 && ws_alloc(&i0, n0 * 8, st) != cudaSuccess) ||
+        (n1 && ws_alloc(&i1, n1 * 8, st) != cudaSuccess) || (vb.span && ws_alloc(&B_dev, vb.span * sizeof(T), st) != cudaSuccess)) {
+        cudaGetLastError(); rc = RBX_ERR_ALLOC;
+    }
+    if (rc == RBX_OK && nnz && cudaMemcpyAsync(vals, vals_h, (size_t) nnz * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK && n0 && cudaMemcpyAsync(i0, idx0_h, n0 * 8, cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK && n1 && cudaMemcpyAsync(i1, idx1_h, n1 * 8, cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK && vb.span && read_B && cudaMemcpyAsync(B_dev, B_host, vb.span * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (rc == RBX_OK) rc = sketch_sparsedata<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s,
+                                                fmt, A_rows, A_cols, nnz, vals, i0, i1, ro_a, co_a, beta, B_dev, ldb, (void*) st);
+    if (rc == RBX_OK && copy_back_view<T>(B_host, B_dev, vb, st) != cudaSuccess) rc = RBX_ERR_CUDA;
+    if (vals) cudaFreeAsync(vals, st);
+    if (i0) cudaFreeAsync(i0, st);
+    if (i1) cudaFreeAsync(i1, st);
+    if (B_dev) cudaFreeAsync(B_dev, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess && rc == RBX_OK) rc = RBX_ERR_CUDA;
+    return rc;
+}
+
 // ---- sparse format conversion -----------------------------------------------------------------------
 template <typename T>
 static int sparse_regroup(char by, char fmt_in, int64_t n_rows, int64_t n_cols, int64_t nnz, const T* vals, const int64_t* idx0,
@@ -833,6 +871,15 @@ int rbx_sketch_sparsedata_##SUF(char side, char layout, char opS, char opA, int6
                                 int64_t co_a, T beta, T* B_dev, int64_t ldb, void* stream) {                                      \
     return sketch_sparsedata<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key,          \
                                 ro_s, co_s, fmt, A_rows, A_cols, nnz, vals_dev, idx0_dev, idx1_dev, ro_a, co_a, beta, B_dev, ldb, stream); \
+}                                                                                                                                 \
+int rbx_host_sketch_sparsedata_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,     \
+                                     int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4],         \
+                                     const uint32_t key[2], int64_t ro_s, int64_t co_s, char fmt, int64_t A_rows, int64_t A_cols, \
+                                     int64_t nnz, const T* vals_host, const int64_t* idx0_host, const int64_t* idx1_host,         \
+                                     int64_t ro_a, int64_t co_a, T beta, T* B_host, int64_t ldb) {                                \
+    return host_sketch_sparsedata<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key,     \
+                                     ro_s, co_s, fmt, A_rows, A_cols, nnz, vals_host, idx0_host, idx1_host, ro_a, co_a, beta,     \
+                                     B_host, ldb);                                                                                \
 }
 RBX_DEF_DENSE(f32, float)
 RBX_DEF_DENSE(f64, double)

@@ -676,6 +676,49 @@ def test_host_pointer_padded_B_is_untouched_outside_the_view(rb, cuda, dt):
     assert np.array_equal(y.numpy()[gap], y0[gap]) and not np.array_equal(y.numpy()[::incy], y0[::incy])
 
 
+@pytest.mark.parametrize("fmt", ["O", "R", "C"])
+def test_host_pointer_sketch_sparse(rb, cuda, fmt):
+    """rbx_host_sketch_sparsedata_*: the sparse matrix and B in host memory give the device call's bits; B as a window of a
+    larger host array (ldb beyond the natural dimension) keeps its padding, with beta == 0 (NaNs in B must not propagate)
+    and with beta != 0; argument errors are reported without touching B"""
+    rng = np.random.default_rng(91)
+    for dt in ("f32", "f64"):
+        npdt = np.float32 if dt == "f32" else np.float64
+        bits = np.uint32 if dt == "f32" else np.uint64
+        for (side, layout, d, n, m, pad, beta) in [("L", "C", 24, 300, 500, 0, 0.0), ("L", "C", 24, 40, 500, 7, 0.0), ("L", "R", 12, 130, 260, 5, -0.5),
+                                                  ("R", "C", 16, 200, 90, 3, 0.0), ("R", "R", 16, 200, 90, 0, 1.5)]:
+            # left: B (d x n) = S (d x m) A (m x n);  right: B (m' x d) = A (m' x n') S (n' x d) with m' = n, n' = m here
+            rowsA, colsA = (m, n) if side == "L" else (n, m)
+            rowsB, colsB = (d, n) if side == "L" else (n, d)
+            Afull = random_sparse(rng, rowsA, colsA, 0.05, npdt)
+            Ad = to_fmt(rb, cuda, Afull, fmt)
+            i0, i1 = Ad._idx()
+            Ah = type(Ad)(Ad.n_rows, Ad.n_cols, Ad.vals.cpu(), i0.cpu(), i1.cpu())
+            ldb = (rowsB if layout == "C" else colsB) + pad
+            B0 = rng.standard_normal(span(layout, rowsB, colsB, ldb)).astype(npdt)
+            if beta == 0.0:
+                B0[::3] = np.nan
+            S = rb.DenseSkOp(rb.DenseDist(d, m) if side == "L" else rb.DenseDist(m, d), 13, dtype=TDT[dt])
+            L, O = rb.Layout(layout), rb.Op
+            Bh, Bd = torch.from_numpy(B0.copy()), torch.from_numpy(B0.copy()).to(cuda)
+            for (A_, B_) in ((Ah, Bh), (Ad, Bd)):
+                if side == "L":
+                    rb.sketch_sparse(L, O.NoTrans, O.NoTrans, d, n, m, 2.0, S, 0, 0, A_, 0, 0, beta, B_, ldb)
+                else:
+                    rb.sketch_sparse(L, O.NoTrans, O.NoTrans, n, d, m, 2.0, A_, 0, 0, S, 0, 0, beta, B_, ldb)
+            got, dev = Bh.numpy(), Bd.cpu().numpy()
+            assert np.array_equal(got.view(bits), dev.view(bits)), (dt, side, layout, fmt, pad)
+            mask = np.ones(len(B0), bool)
+            mask[mat(layout, rowsB, colsB, ldb, np.arange(len(B0))).ravel()] = False
+            assert np.array_equal(got[mask].view(bits), B0[mask].view(bits)) and np.isfinite(got[~mask]).all()
+    # the reference's dimension check (sksp.hh:175-178) comes back as Error before anything is written
+    Bh = torch.full((24 * 300,), 7.0, dtype=torch.float64)
+    with pytest.raises(rb.Error):
+        rb.sketch_sparse(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, 24, 300, 501, 1.0, rb.DenseSkOp(rb.DenseDist(24, 501), 1, dtype=torch.float64),
+                         0, 0, Ah, 0, 0, 0.0, Bh, 24)
+    assert float(Bh.min()) == 7.0 and float(Bh.max()) == 7.0
+
+
 @pytest.mark.parametrize("layout", ["C", "R"])
 def test_host_pointer_pipelined_slabs(rb, cuda, layout):
     """host matrices of >= 1 GiB are sketched slab by slab (copy of slab i+1 overlaps the sketch of slab i, co_s advanced per
