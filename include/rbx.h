@@ -47,6 +47,11 @@ int rbx_stream_synchronize(void* stream);
    (never the default pool the application shares) that keeps up to 1/32 of the device's memory mapped between calls
    (RBX_WS_KEEP_MB overrides); this synchronises the device and returns all of it to the driver. */
 int rbx_trim_workspace(void);
+/* bytes of the current device's private workspace pool: in use now, the most in use at any time since the last reset (the
+   high-water mark: what a call really needed), and mapped now. reset_high != 0 restarts the high-water mark after reading it.
+   No counterpart in the reference (its workspaces are std::vector / new[]); the tests use it to hold the implicit dense
+   sketches to "no allocation proportional to d * m". */
+int rbx_workspace_stats(uint64_t* used_now, uint64_t* used_high, uint64_t* reserved_now, int reset_high);
 
 /* ---- RNG state algebra (host-side, exact) ------------------------------------------------------ */
 /* ctr += n with carry: Random123 array.h incr(); pinned by test/test_basic_rng/test_r123.cc:679-766 */

@@ -1012,6 +1012,26 @@ int rbx_trim_workspace(void) {
     return cudaMemPoolTrimTo(pool, 0) == cudaSuccess ? RBX_OK : RBX_ERR_CUDA;
 }
 
+int rbx_workspace_stats(uint64_t* used_now, uint64_t* used_high, uint64_t* reserved_now, int reset_high) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_NO_DEVICE; }
+    cudaMemPool_t pool = ws_pool(dev);
+    unsigned long long un = 0, uh = 0, rn = 0;
+    if (pool) {
+        if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &un) != cudaSuccess ||
+            cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &uh) != cudaSuccess ||
+            cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &rn) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_CUDA; }
+        if (reset_high) {
+            unsigned long long zero = 0;
+            if (cudaMemPoolSetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &zero) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_CUDA; }
+        }
+    }
+    if (used_now) *used_now = un;
+    if (used_high) *used_high = uh;
+    if (reserved_now) *reserved_now = rn;
+    return RBX_OK;
+}
+
 int rbx_host_fill_sparse_f64_i64(int64_t n_rows, int64_t n_cols, int64_t vec_nnz, char major_axis, const uint32_t ctr[4], const uint32_t key[2],
                                  int64_t* rows_host, int64_t* cols_host, double* vals_host, uint32_t next_ctr[4]) {
     return host_fill_sparse<double, int64_t>(n_rows, n_cols, vec_nnz, major_axis, ctr, key, rows_host, cols_host, vals_host, next_ctr);
