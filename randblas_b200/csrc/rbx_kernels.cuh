@@ -84,9 +84,6 @@ int launch_coo_gather(int64_t nnz, const int64_t* rows, const int64_t* cols, con
 // expand a CSR rowptr / CSC colptr (n_outer + 1 entries) into one outer index per nonzero
 int launch_expand_ptr(int64_t n_outer, const int64_t* ptr, int64_t* outer_idx, cudaStream_t stream);
 
-// dst[l * ldd + j] = src[l + j * lds] for a K x N matrix (makes rows contiguous for the streaming kernels)
-template <typename T> int launch_transpose(const T* src, int64_t K, int64_t N, int64_t lds, T* dst, int64_t ldd, cudaStream_t stream);
-
 // fast SASO path (left sketch, wide Short-axis operator, contiguous rows of X); RBX_ERR_UNSUPPORTED otherwise
 template <typename T>
 int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_t S_cols, int64_t vec_nnz, int64_t ro, int64_t co,

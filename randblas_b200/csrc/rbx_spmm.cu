@@ -1,12 +1,8 @@
-// K4/K5 (general paths): sparse-times-dense products behind lskges/rskges and lsksp3/rsksp3.
-//
-// Replaces left_spmm / right_spmm (spmm_dispatch.hh:48-200) and the OpenMP kernels they select
-// (coo_spmm_impl.hh:79-162, csc_spmm_impl.hh:43-213, csr_spmm_impl.hh:45-156). The reference sorts the
-// COO triplets into CSC order on the host and walks one column of the dense operand per OpenMP task;
-// these kernels take the triplets in any order, apply submatrix filtering and transposition on the fly
-// (set_filtered_coo, coo_spmm_impl.hh:45-75) and accumulate with red.global.add. They are the
-// shape-agnostic fallbacks; rbx_saso.cu holds the conflict-free streaming kernel for the SASO hot case.
-// Both are HBM/L2-bound byte-moving kernels: no tensor cores involved.
+// Small helper kernels shared by the sparse paths: the safe_scal of an output view (util.hh:51-59), the expansion of a CSR /
+// CSC pointer array into one outer index per nonzero (the device-side step of viewing compressed data as COO triplets,
+// spmm_dispatch.hh:48-200) and util::require_symmetric (util.hh:165-188). The products themselves live in rbx_saso.cu (SASO
+// streaming kernel), rbx_spmm_gather.cu (every other sparse operator, deterministic gather) and rbx_spdata.cu (sparse data).
+// (Round 1's atomicAdd scatter lived here; it was replaced by the gather kernels and removed.)
 #include "rbx_kernels.cuh"
 
 namespace rbx {
@@ -34,34 +30,6 @@ int launch_scale_view(T* C, int64_t M, int64_t N, int64_t sc_i, int64_t sc_j, T 
 }
 template int launch_scale_view<float>(float*, int64_t, int64_t, int64_t, int64_t, float, cudaStream_t);
 template int launch_scale_view<double>(double*, int64_t, int64_t, int64_t, int64_t, double, cudaStream_t);
-
-// dst[l * ldd + j] = src[l + j * lds]  (K x N): column-major data re-laid with contiguous rows, 64x64 tiles through smem
-template <typename T>
-__global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ src, int64_t K, int64_t N, int64_t lds, T* __restrict__ dst, int64_t ldd) {
-    __shared__ T tile[64][65];
-    const int64_t l0 = (int64_t) blockIdx.x * 64, j0 = (int64_t) blockIdx.y * 64;
-    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
-    for (int jj = ty; jj < 64; jj += 4) {
-        const int64_t l = l0 + tx, j = j0 + jj;
-        tile[jj][tx] = (l < K && j < N) ? __ldcs(src + l + j * lds) : (T) 0;
-    }
-    __syncthreads();
-    for (int ll = ty; ll < 64; ll += 4) {
-        const int64_t l = l0 + ll, j = j0 + tx;
-        if (l < K && j < N) dst[l * ldd + j] = tile[tx][ll];
-    }
-}
-template <typename T>
-int launch_transpose(const T* src, int64_t K, int64_t N, int64_t lds, T* dst, int64_t ldd, cudaStream_t stream) {
-    if (K <= 0 || N <= 0) return RBX_OK;
-    dim3 grid((unsigned)((K + 63) / 64), (unsigned)((N + 63) / 64));
-    if (grid.y > 65535u) return RBX_ERR_UNSUPPORTED;
-    transpose_kernel<T><<<grid, 256, 0, stream>>>(src, K, N, lds, dst, ldd);
-    count_launch();
-    return check_launch("transpose_kernel");
-}
-template int launch_transpose<float>(const float*, int64_t, int64_t, int64_t, float*, int64_t, cudaStream_t);
-template int launch_transpose<double>(const double*, int64_t, int64_t, int64_t, double*, int64_t, cudaStream_t);
 
 __global__ void __launch_bounds__(256) expand_ptr_kernel(int64_t n_outer, const int64_t* __restrict__ ptr, int64_t* __restrict__ outer_idx) {
     const int lane = threadIdx.x & 31;
