@@ -416,6 +416,9 @@ template <typename T> struct fn {
     static sketch_sparseop_t sketch_sparseop() { return (sketch_sparseop_t) RBX_PICK(T, rbx_sketch_sparseop); }
     static host_sketch_sparseop_t host_sketch_sparseop() { return (host_sketch_sparseop_t) RBX_PICK(T, rbx_host_sketch_sparseop); }
     static spmm_coo_t spmm_coo() { return (spmm_coo_t) RBX_PICK(T, rbx_spmm_coo); }
+    using spmm_csx_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, int64_t, char, const int64_t*, const int64_t*, const T*,
+                               const T*, int64_t, T, T*, int64_t, void*);
+    static spmm_csx_t spmm_csx() { return (spmm_csx_t) RBX_PICK(T, rbx_spmm_csx); }
     static sparsedata_t sparsedata() { return (sparsedata_t) RBX_PICK(T, rbx_sketch_sparsedata); }
     using host_sparsedata_t = int (*)(char, char, char, char, int64_t, int64_t, int64_t, T, int64_t, int64_t, char, char, const uint32_t*, const uint32_t*,
                                       int64_t, int64_t, char, int64_t, int64_t, int64_t, const T*, const int64_t*, const int64_t*, int64_t, int64_t, T, T*, int64_t);
@@ -841,6 +844,14 @@ inline void left_spmm(blas::Layout layout, blas::Op opA, blas::Op opB, int64_t d
     sp_arrays(A, fmt, i0, n0, i1, n1);
     if (fmt == 'O') { randblas_require(A.n_rows >= rows_sub + ro_a); randblas_require(A.n_cols >= cols_sub + co_a); }     // :94-96
     else { randblas_require(A.n_rows == rows_sub); randblas_require(A.n_cols == cols_sub); randblas_require(ro_a == 0); randblas_require(co_a == 0); }  // :97-104
+    if constexpr (std::is_same<typename SpMat::index_t, int64_t>::value) {
+        if (fmt != 'O' && device_pointers()) {
+            // device-resident CSR / CSC: the arrays go down as they are (used in place when compressed along the output axis)
+            check(::RandBLAS::detail::fn<T>::spmm_csx()('L', ch(layout), ch(opA), ch(opB), d, n, m, alpha, A.n_rows, A.n_cols, A.nnz, fmt,
+                                                        fmt == 'R' ? i0 : i1, fmt == 'R' ? i1 : i0, A.vals, B, ldb, beta, C, ldc, current_stream()), "left_spmm");
+            return;
+        }
+    }
     detail_spmm::DevCoo<T> dc;
     detail_spmm::to_dev_coo<T>(A, dc);
     auto call = ::RandBLAS::detail::fn<T>::spmm_coo();

@@ -181,6 +181,18 @@ int rbx_spmm_coo_f64(char side, char layout, char opS, char opA, int64_t p0, int
                      int64_t S_rows, int64_t S_cols, int64_t nnz, const int64_t* rows_dev, const int64_t* cols_dev, const double* vals_dev,
                      int64_t ro_s, int64_t co_s, const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
 
+/* CSR ('R': ptr = rowptr, idx = colidxs) or CSC ('C': ptr = colptr, idx = rowidxs) operand times dense: left_spmm / right_spmm
+ * with a CSRMatrix / CSCMatrix, spmm_dispatch.hh:48-200 + csr_spmm_impl.hh:45-156 / csc_spmm_impl.hh:43-213. The operand is
+ * taken whole (dimensions equal to the product's, spmm_dispatch.hh:97-104). An operand compressed along the product's output
+ * axis (CSR not transposed, CSC transposed) is used in place -- no regrouping, no copy; the other two cases regroup as
+ * rbx_spmm_coo does. int64 indices, index_base Zero. */
+int rbx_spmm_csx_f32(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, float alpha,
+                     int64_t S_rows, int64_t S_cols, int64_t nnz, char fmt, const int64_t* ptr_dev, const int64_t* idx_dev, const float* vals_dev,
+                     const float* A_dev, int64_t lda, float beta, float* B_dev, int64_t ldb, void* stream);
+int rbx_spmm_csx_f64(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, double alpha,
+                     int64_t S_rows, int64_t S_cols, int64_t nnz, char fmt, const int64_t* ptr_dev, const int64_t* idx_dev, const double* vals_dev,
+                     const double* A_dev, int64_t lda, double beta, double* B_dev, int64_t ldb, void* stream);
+
 /* ---- index sampling utilities, util.hh:257-334 (same Philox + uneg11 stream as the reference, bit for bit) ----
  * rbx_sample_indices_iid_uniform: util::sample_indices_iid_uniform (util.hh:311-334), k samples of {0..n-1};
  * rbx_sample_indices_iid_*:       util::sample_indices_iid (util.hh:284-305), lower_bound in a device-resident cdf;

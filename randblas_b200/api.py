@@ -488,12 +488,16 @@ def left_spmm(layout, opA, opB, d, n, m, alpha, A, ro_a, co_a, B, ldb, beta, C, 
     for a COOMatrix / CSRMatrix / CSCMatrix A on the device. Output-stationary gather, no atomics (rbx_spmm_coo_*)."""
     if A.fmt != "O" and (ro_a != 0 or co_a != 0):
         raise Error("CSR / CSC operands are taken whole (spmm_dispatch.hh:97-104)")
-    rows, cols, vals = _coo_triplets(A)
     dt = C.dtype
+    if A.fmt != "O":
+        # compressed operands go down as they are: used in place when compressed along the output axis (rbx_spmm_csx_*)
+        ptr, idx = (A.rowptr, A.colidxs) if A.fmt == "R" else (A.colptr, A.rowidxs)
+        _call(f"rbx_spmm_csx_{_suf(dt)}", b"L", _c(layout), _c(opA), _c(opB), d, n, m, _scalar(dt, alpha), A.n_rows, A.n_cols, A.nnz,
+              A.fmt.encode(), _ptr(ptr), _ptr(idx), _ptr(A.vals), _ptr(B), ldb, _scalar(dt, beta), _ptr(C), ldc, _stream(C))
+        return
+    rows, cols, vals = _coo_triplets(A)
     _call(f"rbx_spmm_coo_{_suf(dt)}", b"L", _c(layout), _c(opA), _c(opB), d, n, m, _scalar(dt, alpha), A.n_rows, A.n_cols, A.nnz,
           _ptr(rows), _ptr(cols), _ptr(vals), ro_a, co_a, _ptr(B), ldb, _scalar(dt, beta), _ptr(C), ldc, _stream(C))
-    if A.fmt != "O":
-        torch.cuda.current_stream(C.device).synchronize()      # the expanded index array is released on return
 
 
 def right_spmm(layout, opA, opB, m, d, n, alpha, A, lda, B, ro_b, co_b, beta, C, ldc):

@@ -493,6 +493,34 @@ static int spmm_coo(char side, char layout, char opS, char opA, int64_t p0, int6
                                 A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
 }
 
+// left_spmm / right_spmm with a CSR ('R') or CSC ('C') operand (spmm_dispatch.hh:48-200; the reference takes compressed operands
+// whole, :97-104). When the operand is compressed along the output axis of the product -- CSR not transposed, CSC transposed --
+// its arrays are used as they are: no regrouping, no copy. Otherwise the pointer array is expanded to one outer index per
+// nonzero and the triplets take the regrouping path of spmm_coo.
+template <typename T>
+static int spmm_csx(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
+                    int64_t S_rows, int64_t S_cols, int64_t nnz, char fmt, const int64_t* ptr, const int64_t* idx, const T* vals,
+                    const T* A, int64_t lda, T beta, T* B, int64_t ldb, void* stream) {
+    SketchShape s;
+    RBX_TRY(sketch_shape(side, layout, opS, opA, p0, p1, p2, lda, ldb, true, &s));
+    RBX_REQUIRE((fmt == 'R' || fmt == 'C') && nnz >= 0);
+    RBX_REQUIRE(S_rows == s.rows_sub && S_cols == s.cols_sub);               // spmm_dispatch.hh:97-104 (compressed: ==, no offsets)
+    RBX_NEED_DEVICE();
+    cudaStream_t st = (cudaStream_t) stream;
+    const bool direct = (fmt == 'R') ? !s.s_trans : s.s_trans;
+    if (direct)
+        return launch_csx_gather<T>(ptr, idx, vals, nnz, s.M, s.N, s.K, alpha, A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
+    if (nnz == 0 || alpha == (T) 0) return launch_scale_view<T>(B, s.M, s.N, s.sc_i, s.sc_j, beta, st);
+    int64_t* outer = nullptr;
+    if (ws_alloc(&outer, (size_t) nnz * 8, st) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    int rc = launch_expand_ptr(fmt == 'R' ? S_rows : S_cols, ptr, outer, st);
+    if (rc == RBX_OK)
+        rc = launch_coo_gather<T>(nnz, fmt == 'R' ? outer : idx, fmt == 'R' ? idx : outer, vals, s.s_trans, 0, 0, s.M, s.N, s.K, alpha,
+                                  A, s.sx_l, s.sx_j, beta, B, s.sc_i, s.sc_j, st);
+    cudaFreeAsync(outer, st);
+    return rc;
+}
+
 template <typename T>
 static int sketch_sparseop(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,
                            int64_t S_rows, int64_t S_cols, int64_t vec_nnz, char major_axis, const uint32_t* ctr, const uint32_t* key,
@@ -863,6 +891,12 @@ int rbx_spmm_coo_##SUF(char side, char layout, char opS, char opA, int64_t p0, i
                        int64_t ro_s, int64_t co_s, const T* A_dev, int64_t lda, T beta, T* B_dev, int64_t ldb, void* stream) {    \
     return spmm_coo<T, int64_t>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, nnz, rows_dev, cols_dev, vals_dev,     \
                                 ro_s, co_s, A_dev, lda, beta, B_dev, ldb, stream);                                                \
+}                                                                                                                                 \
+int rbx_spmm_csx_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha, int64_t S_rows,   \
+                       int64_t S_cols, int64_t nnz, char fmt, const int64_t* ptr_dev, const int64_t* idx_dev, const T* vals_dev,  \
+                       const T* A_dev, int64_t lda, T beta, T* B_dev, int64_t ldb, void* stream) {                                \
+    return spmm_csx<T>(side, layout, opS, opA, p0, p1, p2, alpha, S_rows, S_cols, nnz, fmt, ptr_dev, idx_dev, vals_dev,           \
+                       A_dev, lda, beta, B_dev, ldb, stream);                                                                     \
 }                                                                                                                                 \
 int rbx_sketch_sparsedata_##SUF(char side, char layout, char opS, char opA, int64_t p0, int64_t p1, int64_t p2, T alpha,          \
                                 int64_t D_rows, int64_t D_cols, char family, char major_axis, const uint32_t ctr[4],              \

@@ -81,6 +81,11 @@ int launch_coo_gather(int64_t nnz, const int64_t* rows, const int64_t* cols, con
                       int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
                       T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
 
+// the same product for an operand already compressed along the output axis (its ptr / idx / vals arrays are the segments)
+template <typename T>
+int launch_csx_gather(const int64_t* ptr, const int64_t* lidx, const T* vals, int64_t nnz, int64_t M, int64_t N, int64_t K, T alpha,
+                      const T* X, int64_t sx_l, int64_t sx_j, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream);
+
 // expand a CSR rowptr / CSC colptr (n_outer + 1 entries) into one outer index per nonzero
 int launch_expand_ptr(int64_t n_outer, const int64_t* ptr, int64_t* outer_idx, cudaStream_t stream);
 

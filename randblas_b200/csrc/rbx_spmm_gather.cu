@@ -112,6 +112,36 @@ __global__ void __launch_bounds__(32 * CG_WPB) coo_gather_cols_kernel(const CooG
     }
 }
 
+// the gather kernels over ready-made segments: row i of the output owns entries [ptr[i * nlc], ptr[(i + 1) * nlc])
+template <typename T>
+static int run_gather_segments(const int64_t* ptr, const int64_t* lidx, const T* v, int64_t nlc, int64_t M, int64_t N, T alpha,
+                               const T* X, int64_t sx_l, int64_t sx_j, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
+    int rc = RBX_OK;
+    CooGatherArgs<T> a;
+    a.ptr = ptr; a.lidx = lidx; a.vals = v; a.nlc = nlc; a.M = M; a.N = N; a.X = X; a.sx_l = sx_l; a.sx_j = sx_j;
+    a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j;
+    const int64_t by = (M + CG_WPB - 1) / CG_WPB;
+    // grid.y is limited to 65535: tile the rows in launches of that many blocks
+    for (int64_t y0 = 0; y0 < by && rc == RBX_OK; y0 += 65535) {
+        const int64_t ny = (by - y0 < 65535) ? by - y0 : 65535;
+        CooGatherArgs<T> b = a;
+        b.ptr = a.ptr + y0 * CG_WPB * nlc; b.M = (M - y0 * CG_WPB < ny * CG_WPB) ? M - y0 * CG_WPB : ny * CG_WPB;
+        b.C = a.C + y0 * CG_WPB * sc_i;
+        if (sx_j == 1 || sx_l != 1) {
+            const int64_t bx = (N + 127) / 128;
+            if (bx > 0x7fffffffLL) { rc = RBX_ERR_UNSUPPORTED; break; }
+            coo_gather_rows_kernel<T><<<dim3((unsigned) bx, (unsigned) ny), 32 * CG_WPB, 0, stream>>>(b);
+        } else {
+            const int64_t bx = (N + 3) / 4;
+            if (bx > 0x7fffffffLL) { rc = RBX_ERR_UNSUPPORTED; break; }
+            coo_gather_cols_kernel<T><<<dim3((unsigned) bx, (unsigned) ny), 32 * CG_WPB, 0, stream>>>(b);
+        }
+        count_launch();
+        rc = check_launch("coo_gather_kernel");
+    }
+    return rc;
+}
+
 template <typename T>
 int launch_coo_gather(int64_t nnz, const int64_t* rows, const int64_t* cols, const T* vals, bool trans, int64_t ro, int64_t co,
                       int64_t M, int64_t N, int64_t K, T alpha, const T* X, int64_t sx_l, int64_t sx_j,
@@ -136,28 +166,7 @@ int launch_coo_gather(int64_t nnz, const int64_t* rows, const int64_t* cols, con
     int64_t *ptr = nullptr, *lidx = nullptr; T* v = nullptr;
     int rc = spd_group_by_column<T>(nnz, rows, cols, vals, !trans, ro, co, K, M, &ptr, &lidx, &v, stream, lc_shift, nlc);
     if (rc != RBX_OK) return rc;
-    CooGatherArgs<T> a;
-    a.ptr = ptr; a.lidx = lidx; a.vals = v; a.nlc = nlc; a.M = M; a.N = N; a.X = X; a.sx_l = sx_l; a.sx_j = sx_j;
-    a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j;
-    const int64_t by = (M + CG_WPB - 1) / CG_WPB;
-    // grid.y is limited to 65535: tile the rows in launches of that many blocks
-    for (int64_t y0 = 0; y0 < by && rc == RBX_OK; y0 += 65535) {
-        const int64_t ny = (by - y0 < 65535) ? by - y0 : 65535;
-        CooGatherArgs<T> b = a;
-        b.ptr = a.ptr + y0 * CG_WPB * nlc; b.M = (M - y0 * CG_WPB < ny * CG_WPB) ? M - y0 * CG_WPB : ny * CG_WPB;
-        b.C = a.C + y0 * CG_WPB * sc_i;
-        if (sx_j == 1 || sx_l != 1) {
-            const int64_t bx = (N + 127) / 128;
-            if (bx > 0x7fffffffLL) { rc = RBX_ERR_UNSUPPORTED; break; }
-            coo_gather_rows_kernel<T><<<dim3((unsigned) bx, (unsigned) ny), 32 * CG_WPB, 0, stream>>>(b);
-        } else {
-            const int64_t bx = (N + 3) / 4;
-            if (bx > 0x7fffffffLL) { rc = RBX_ERR_UNSUPPORTED; break; }
-            coo_gather_cols_kernel<T><<<dim3((unsigned) bx, (unsigned) ny), 32 * CG_WPB, 0, stream>>>(b);
-        }
-        count_launch();
-        rc = check_launch("coo_gather_kernel");
-    }
+    rc = run_gather_segments<T>(ptr, lidx, v, nlc, M, N, alpha, X, sx_l, sx_j, beta, C, sc_i, sc_j, stream);
     cudaFreeAsync(ptr, stream); cudaFreeAsync(lidx, stream); cudaFreeAsync(v, stream);
     return rc;
 }
@@ -165,5 +174,20 @@ template int launch_coo_gather<float>(int64_t, const int64_t*, const int64_t*, c
                                       float, const float*, int64_t, int64_t, float, float*, int64_t, int64_t, cudaStream_t);
 template int launch_coo_gather<double>(int64_t, const int64_t*, const int64_t*, const double*, bool, int64_t, int64_t, int64_t, int64_t, int64_t,
                                        double, const double*, int64_t, int64_t, double, double*, int64_t, int64_t, cudaStream_t);
+
+// The same product for an operand that is already compressed along the output axis (CSR used as is, CSC used transposed):
+// its pointer / index / value arrays ARE the segments, so nothing is regrouped or copied. Entries of a row are summed in
+// storage order (fixed, so the result is still bitwise reproducible).
+template <typename T>
+int launch_csx_gather(const int64_t* ptr, const int64_t* lidx, const T* vals, int64_t nnz, int64_t M, int64_t N, int64_t K, T alpha,
+                      const T* X, int64_t sx_l, int64_t sx_j, T beta, T* C, int64_t sc_i, int64_t sc_j, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return RBX_OK;
+    if (alpha == (T) 0 || nnz <= 0 || K <= 0) return launch_scale_view<T>(C, M, N, sc_i, sc_j, beta, stream);
+    return run_gather_segments<T>(ptr, lidx, vals, 1, M, N, alpha, X, sx_l, sx_j, beta, C, sc_i, sc_j, stream);
+}
+template int launch_csx_gather<float>(const int64_t*, const int64_t*, const float*, int64_t, int64_t, int64_t, int64_t, float, const float*, int64_t,
+                                      int64_t, float, float*, int64_t, int64_t, cudaStream_t);
+template int launch_csx_gather<double>(const int64_t*, const int64_t*, const double*, int64_t, int64_t, int64_t, int64_t, double, const double*, int64_t,
+                                       int64_t, double, double*, int64_t, int64_t, cudaStream_t);
 
 }  // namespace rbx
