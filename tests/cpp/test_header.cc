@@ -290,6 +290,84 @@ static void test_sparse_surface() {
     CHECK(pad_ok && val_ok);
 }
 
+// device_pointers() mode: every array the caller passes already lives in device memory (rbx_malloc); the same calls give the
+// host-mode results -- fill_dense, dense and sparse-operator sketch_general, left_spmm on a CSR / CSC matrix held on the device
+// (used in place when compressed along the output axis, rbx_spmm_csx_*), sketch_sparse
+template <typename T> static T* to_dev(const std::vector<T>& h) {
+    void* p = nullptr;
+    CHECK(rbx_malloc(&p, h.size() * sizeof(T)) == 0);
+    CHECK(rbx_memcpy_h2d(p, h.data(), h.size() * sizeof(T), nullptr) == 0);
+    return (T*) p;
+}
+template <typename T> static std::vector<T> to_host(const T* d, size_t n) {
+    std::vector<T> h(n);
+    CHECK(rbx_memcpy_d2h(h.data(), d, n * sizeof(T), nullptr) == 0);
+    CHECK(rbx_stream_synchronize(nullptr) == 0);
+    return h;
+}
+static void test_device_pointer_mode() {
+    const int64_t d = 24, m = 700, n = 40;
+    std::vector<double> A = randmat(m * n, 31), Bh(d * n, 0.0), B0(d * n, 0.0);
+    DenseSkOp<double> Sd(DenseDist(d, m), RNGState<>(4));
+    SparseSkOp<double> Ss({ d, m, 4, MajorAxis::Short }, RNGState<>(6));
+    // host-mode results first
+    std::vector<double> Wd(d * n, 0.0), Ws(d * n, 0.0), G(m * n);
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, Sd, A.data(), m, 0.0, Wd.data(), d);
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, Ss, A.data(), m, 0.0, Ws.data(), d);
+    fill_dense(DenseDist(m, n), G.data(), RNGState<>(31));
+    // a sparse data matrix (m x n, every third entry of a few columns) as CSR and CSC on the host
+    std::vector<double> sv; std::vector<int64_t> sr, sc;
+    for (int64_t i = 0; i < m; ++i) for (int64_t j = (i % 3); j < n; j += 5) { sr.push_back(i); sc.push_back(j); sv.push_back(std::cos(0.1 * i + j)); }
+    const int64_t nnz = (int64_t) sv.size();
+    std::vector<int64_t> rowptr(m + 1, 0), colptr(n + 1, 0);
+    for (int64_t e = 0; e < nnz; ++e) { ++rowptr[sr[e] + 1]; ++colptr[sc[e] + 1]; }
+    for (int64_t i = 0; i < m; ++i) rowptr[i + 1] += rowptr[i];
+    for (int64_t j = 0; j < n; ++j) colptr[j + 1] += colptr[j];
+    std::vector<int64_t> csc_rows(nnz); std::vector<double> csc_vals(nnz); std::vector<int64_t> cur(colptr.begin(), colptr.end() - 1);
+    for (int64_t e = 0; e < nnz; ++e) { const int64_t p = cur[sc[e]]++; csc_rows[p] = sr[e]; csc_vals[p] = sv[e]; }
+    // reference products on the host (dense loops): P1 = Asp^T (n x m) * X (m x 6), P2 = Asp (m x n) * Y (n x 6)
+    const int64_t k = 6;
+    std::vector<double> X = randmat(m * k, 77), Y = randmat(n * k, 78), P1(n * k, 0.0), P2(m * k, 0.0);
+    for (int64_t e = 0; e < nnz; ++e) for (int64_t c = 0; c < k; ++c) { P1[sc[e] + c * n] += sv[e] * X[sr[e] + c * m]; P2[sr[e] + c * m] += sv[e] * Y[sc[e] + c * n]; }
+
+    device_pointers() = true;
+    double *dA = to_dev(A), *dB = to_dev(B0), *dG = to_dev(G), *dX = to_dev(X), *dY = to_dev(Y);
+    double *dP1 = to_dev(P1), *dP2 = to_dev(P2);           // overwritten below (beta == 0)
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, Sd, dA, m, 0.0, dB, d);
+    CHECK(max_rel(to_host(dB, d * n), Wd) < 1e-13);
+    sketch_general(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, Ss, dA, m, 0.0, dB, d);
+    CHECK(max_rel(to_host(dB, d * n), Ws) < 1e-13);
+    fill_dense(DenseDist(m, n), dG, RNGState<>(31));
+    CHECK(bits_equal(to_host(dG, m * n), G));
+    {   // CSR and CSC views over device arrays (the containers do not own them)
+        double *dv = to_dev(sv), *dcv = to_dev(csc_vals);
+        int64_t *drp = to_dev(rowptr), *dci = to_dev(sc), *dcp = to_dev(colptr), *dri = to_dev(csc_rows);
+        sparse_data::CSRMatrix<double> R(m, n, nnz, dv, drp, dci);
+        sparse_data::CSCMatrix<double> C(m, n, nnz, dcv, dri, dcp);
+        std::vector<double> got;
+        left_spmm(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, m, k, n, 1.0, R, 0, 0, dY, n, 0.0, dP2, m);     // CSR in place
+        got = to_host(dP2, m * k); CHECK(max_rel(got, P2) < 1e-13);
+        left_spmm(blas::Layout::ColMajor, blas::Op::Trans, blas::Op::NoTrans, n, k, m, 1.0, C, 0, 0, dX, m, 0.0, dP1, n);       // CSC^T in place
+        got = to_host(dP1, n * k); CHECK(max_rel(got, P1) < 1e-13);
+        left_spmm(blas::Layout::ColMajor, blas::Op::Trans, blas::Op::NoTrans, n, k, m, 1.0, R, 0, 0, dX, m, 0.0, dP1, n);       // CSR^T: regrouped
+        got = to_host(dP1, n * k); CHECK(max_rel(got, P1) < 1e-13);
+        left_spmm(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, m, k, n, 1.0, C, 0, 0, dY, n, 0.0, dP2, m);     // CSC: regrouped
+        got = to_host(dP2, m * k); CHECK(max_rel(got, P2) < 1e-13);
+        // sketch_sparse with the matrix on the device against the host-mode call
+        DenseSkOp<double> S2(DenseDist(d, m), RNGState<>(8));
+        std::vector<double> Wsp(d * n, 0.0);
+        device_pointers() = false;
+        sparse_data::CSRMatrix<double> Rh(m, n, nnz, sv.data(), rowptr.data(), sc.data());
+        sketch_sparse(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S2, 0, 0, Rh, 0, 0, 0.0, Wsp.data(), d);
+        device_pointers() = true;
+        sketch_sparse(blas::Layout::ColMajor, blas::Op::NoTrans, blas::Op::NoTrans, d, n, m, 1.0, S2, 0, 0, R, 0, 0, 0.0, dB, d);
+        CHECK(max_rel(to_host(dB, d * n), Wsp) < 1e-13);
+        rbx_free(dv); rbx_free(dcv); rbx_free(drp); rbx_free(dci); rbx_free(dcp); rbx_free(dri);
+    }
+    device_pointers() = false;
+    rbx_free(dA); rbx_free(dB); rbx_free(dG); rbx_free(dX); rbx_free(dY); rbx_free(dP1); rbx_free(dP2);
+}
+
 int main() {
     if (rbx_device_count() < 1) { std::printf("no CUDA device: the product path has no CPU fallback\n"); return 77; }
     test_fill_dense();
@@ -300,6 +378,7 @@ int main() {
     test_index_sampling();
     test_rngstate_surface();
     test_sparse_surface();
+    test_device_pointer_mode();
     std::printf(failures ? "FAILED (%d)\n" : "OK\n", failures);
     return failures ? 1 : 0;
 }
