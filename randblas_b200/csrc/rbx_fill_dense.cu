@@ -52,15 +52,24 @@ __global__ void __launch_bounds__(256) fill_dense_kernel(T* __restrict__ out, co
 
     const int64_t tid = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= p.items) return;
+    // only the uniform family is ever scaled (sqrt(3), dense_skops.hh:512); for the Gaussian family the flag folds to a constant
+    // and the four predicated multiplies leave the loop
+    if (FAMILY == 'G') do_scale = false;
     if (LINEAR) {
         double kl[14];
         if (FAMILY == 'G') hoist_bm_consts(kl);
         const Ctr128 base = ctr_add(p.ctr, (uint64_t)(p.r0 * p.W));
         const int64_t stride = (int64_t) gridDim.x * blockDim.x;
-        for (int64_t it = tid; it < p.items; it += stride) {
-            const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
-            store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, do_scale), cast_scale<T>(v.y, scale, do_scale),
-                      cast_scale<T>(v.z, scale, do_scale), cast_scale<T>(v.w, scale, do_scale));
+        if (do_scale) {
+            for (int64_t it = tid; it < p.items; it += stride) {
+                const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
+                store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, true), cast_scale<T>(v.y, scale, true), cast_scale<T>(v.z, scale, true), cast_scale<T>(v.w, scale, true));
+            }
+        } else {
+            for (int64_t it = tid; it < p.items; it += stride) {
+                const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
+                store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, false), cast_scale<T>(v.y, scale, false), cast_scale<T>(v.z, scale, false), cast_scale<T>(v.w, scale, false));
+            }
         }
         return;
     }
