@@ -41,6 +41,19 @@ template <> __device__ __forceinline__ void store4<double>(double* p, double a, 
     __stcs(reinterpret_cast<double2*>(p) + 1, make_double2(c, d));
 }
 
+// the whole-row fill's loop: item k of this thread is counter (lo + k * stride, hi) and float4 dst + 4 * k * stride
+template <typename T, char FAMILY, bool SCALE>
+__device__ __forceinline__ void linear_loop(T* __restrict__ dst, uint64_t lo, uint32_t c2, uint32_t c3, const Key64 key, int n_it, int64_t stride,
+                                            T scale, const double* __restrict__ tab, const double* __restrict__ kl) {
+#pragma unroll 1
+    for (int k = 0; k < n_it; ++k) {
+        const float4 v = generate4<FAMILY>(philox4x32_10((uint32_t) lo, (uint32_t)(lo >> 32), c2, c3, key.v[0], key.v[1]), tab, kl);
+        store4<T>(dst, cast_scale<T>(v.x, scale, SCALE), cast_scale<T>(v.y, scale, SCALE), cast_scale<T>(v.z, scale, SCALE), cast_scale<T>(v.w, scale, SCALE));
+        lo += (uint64_t) stride;
+        dst += 4 * stride;
+    }
+}
+
 // VEC: every block of every row is complete, unit column stride, and 4-element aligned in memory.
 // LINEAR (with VEC): the window is whole parent rows stored back to back, so item k is counter k and float4 k -- the
 // whole-matrix fill (BASELINE config 3). The general walk's 64-bit (row, block) bookkeeping with its wrap correction is a
@@ -60,16 +73,21 @@ __global__ void __launch_bounds__(256) fill_dense_kernel(T* __restrict__ out, co
         if (FAMILY == 'G') hoist_bm_consts(kl);
         const Ctr128 base = ctr_add(p.ctr, (uint64_t)(p.r0 * p.W));
         const int64_t stride = (int64_t) gridDim.x * blockDim.x;
-        if (do_scale) {
-            for (int64_t it = tid; it < p.items; it += stride) {
-                const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
-                store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, true), cast_scale<T>(v.y, scale, true), cast_scale<T>(v.z, scale, true), cast_scale<T>(v.w, scale, true));
-            }
-        } else {
-            for (int64_t it = tid; it < p.items; it += stride) {
-                const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
-                store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, false), cast_scale<T>(v.y, scale, false), cast_scale<T>(v.z, scale, false), cast_scale<T>(v.w, scale, false));
-            }
+        // The 128-bit counter of item `it` is base + it. Unless the low 64 bits wrap inside this launch (they do once in 2^64
+        // counters; the general loop below takes that case), the high words are constants and the low words a running 64-bit
+        // sum: no carry chain, a 32-bit trip count and a running output pointer. The uniform loop is bound by the integer ALU
+        // pipe (20 LOP3 of Philox + bookkeeping, two cycles each), so every add / compare taken out of it shows.
+        const uint64_t base_lo = ((uint64_t) base.v[1] << 32) | base.v[0];
+        if (base_lo + (uint64_t) p.items >= base_lo) {
+            const int n_it = (int)((p.items - tid + stride - 1) / stride);
+            if (do_scale) linear_loop<T, FAMILY, true>(out + 4 * tid, base_lo + (uint64_t) tid, base.v[2], base.v[3], p.key, n_it, stride, scale, tab, kl);
+            else          linear_loop<T, FAMILY, false>(out + 4 * tid, base_lo + (uint64_t) tid, base.v[2], base.v[3], p.key, n_it, stride, scale, tab, kl);
+            return;
+        }
+        for (int64_t it = tid; it < p.items; it += stride) {
+            const float4 v = generate4<FAMILY>(philox4x32_10(ctr_add(base, (uint64_t) it), p.key), tab, kl);
+            store4<T>(out + 4 * it, cast_scale<T>(v.x, scale, do_scale), cast_scale<T>(v.y, scale, do_scale),
+                      cast_scale<T>(v.z, scale, do_scale), cast_scale<T>(v.w, scale, do_scale));
         }
         return;
     }

@@ -152,6 +152,21 @@ def test_fill_dense_large_counter_offsets(rb, cuda):
         assert np.array_equal(bits(w[: nr * nc].cpu().numpy()), bits(exp))
 
 
+@pytest.mark.parametrize("fam", ["G", "U"])
+def test_fill_dense_seed_counters_that_carry_inside_the_fill(rb, cuda, fam):
+    """whole-matrix fills (the linear loop) from seed states whose counter words overflow in the middle of the fill: word 0
+    into word 1 (running 64-bit sum), nonzero high words (loop constants), and the low 64 bits wrapping into word 2 (the loop
+    with the full 128-bit add); both output precisions; the returned next state carries too (base.hh:215-232)"""
+    n_rows, n_cols = 96, 1000                       # 24 000 counters
+    for ctr in ([0xFFFFFF00, 0, 0, 0], [0xFFFFF000, 0xFFFFFFFF, 5, 9], [0xFFFFC000, 0xFFFFFFFF, 0xFFFFFFFF, 3], [7, 1, 0xFFFFFFFF, 0xFFFFFFFF]):
+        for dt, tdt in (("f32", torch.float32), ("f64", torch.float64)):
+            buf = torch.empty(n_rows * n_cols, dtype=tdt, device=cuda)
+            nxt = rb.fill_dense(rb.DenseDist(n_rows, n_cols, fam), buf, rb.RNGState(11, ctr))
+            rc, exp, enxt = ol.fill_dense(dt, "R", n_rows, n_cols, fam, "L", n_rows, n_cols, 0, 0, ctr, [11, 0])
+            assert rc == 0 and np.array_equal(bits(buf.cpu().numpy()), bits(exp)), (fam, dt, ctr)
+            assert list(nxt.counter) == list(enxt)
+
+
 def test_fill_dense_2pow28_tiles_vs_oracle(rb, cuda):
     """a 2^28-entry Gaussian fill (16384 x 16384): full-buffer determinism + 32 random 64x64 tiles bitwise vs the oracle"""
     n = 16384
