@@ -41,11 +41,15 @@ template <> __device__ __forceinline__ void store4<double>(double* p, double a, 
     __stcs(reinterpret_cast<double2*>(p) + 1, make_double2(c, d));
 }
 
+#ifndef RBX_FILL_UNROLL
+#define RBX_FILL_UNROLL 4      // measured: 1 -> 4 gives +2 % for both families (loop bookkeeping amortised)
+#endif
+constexpr int kFillUnroll = RBX_FILL_UNROLL;
 // the whole-row fill's loop: item k of this thread is counter (lo + k * stride, hi) and float4 dst + 4 * k * stride
 template <typename T, char FAMILY, bool SCALE>
 __device__ __forceinline__ void linear_loop(T* __restrict__ dst, uint64_t lo, uint32_t c2, uint32_t c3, const Key64 key, int n_it, int64_t stride,
                                             T scale, const double* __restrict__ tab, const double* __restrict__ kl) {
-#pragma unroll 1
+#pragma unroll kFillUnroll
     for (int k = 0; k < n_it; ++k) {
         const float4 v = generate4<FAMILY>(philox4x32_10((uint32_t) lo, (uint32_t)(lo >> 32), c2, c3, key.v[0], key.v[1]), tab, kl);
         store4<T>(dst, cast_scale<T>(v.x, scale, SCALE), cast_scale<T>(v.y, scale, SCALE), cast_scale<T>(v.z, scale, SCALE), cast_scale<T>(v.w, scale, SCALE));
