@@ -402,8 +402,63 @@ static int tc_launch(const GemmOperands<float>& g, char mode, const float* Sx, i
     return rc;
 }
 
+// dst[j * pitch + l] = X[l * sx_l + j] for a kl x N piece of data whose rows l are the contiguous ones (unit stride along j):
+// 64 x 64 tiles through shared memory, both sides coalesced
+__global__ void __launch_bounds__(256) tc_kmajor_copy_kernel(const float* __restrict__ src, int64_t kl, int64_t N, int64_t sx_l,
+                                                             float* __restrict__ dst, int64_t pitch) {
+    __shared__ float tile[64][65];
+    const int64_t l0 = (int64_t) blockIdx.x * 64, j0 = (int64_t) blockIdx.y * 64;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    for (int ll = ty; ll < 64; ll += 4) {
+        const int64_t l = l0 + ll, j = j0 + tx;
+        tile[ll][tx] = (l < kl && j < N) ? __ldcs(src + l * sx_l + j) : 0.f;
+    }
+    __syncthreads();
+    for (int jj = ty; jj < 64; jj += 4) {
+        const int64_t l = l0 + tx, j = j0 + jj;
+        if (l < kl && j < N) dst[j * pitch + l] = tile[tx][jj];
+    }
+}
+
+// Data with unit stride along j instead of along the contraction axis (e.g. RowMajor A in a left sketch, ColMajor A in a
+// right sketch): the tcgen05 kernel wants K-major tiles, so the data is copied chunk by chunk along k into a k-contiguous
+// workspace (at most 512 MB, whatever K is) and every chunk takes the normal path with the operator window advanced and
+// beta = 1 after the first. The copy is one extra pass over A (0.1 ms per 268 MB) against a 16x slower SIMT fallback.
+static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream) {
+    if (g.N > 65535ll * 64) return RBX_ERR_UNSUPPORTED;
+    int64_t budget = (int64_t) 512 << 20;
+    if (const char* ev = getenv("RBX_TC_COPY_MB")) { const int64_t v = atoll(ev); if (v >= 1) budget = v << 20; }     // tests: several chunks at small sizes
+    int64_t kc = (budget / (4 * g.N)) / 32 * 32;
+    if (kc < 512) return RBX_ERR_UNSUPPORTED;
+    const int64_t nch = (g.K + kc - 1) / kc;
+    kc = ((g.K + nch - 1) / nch + 31) / 32 * 32;                          // balanced chunks: none is shorter than kc / 2
+    float* ws = nullptr;
+    if (ws_alloc(&ws, sizeof(float) * (size_t) g.N * (size_t) kc, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    int rc = RBX_OK;
+    for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kc) {
+        const int64_t kl = (l0 + kc <= g.K) ? kc : g.K - l0;
+        dim3 grid((unsigned)((kl + 63) / 64), (unsigned)((g.N + 63) / 64));
+        tc_kmajor_copy_kernel<<<grid, 256, 0, stream>>>(g.X + l0 * g.sx_l, kl, g.N, g.sx_l, ws, kc);
+        count_launch();
+        rc = check_launch("tc_kmajor_copy_kernel");
+        if (rc != RBX_OK) break;
+        GemmOperands<float> gp = g;
+        gp.X = ws; gp.sx_l = 1; gp.sx_j = kc; gp.K = kl;
+        gp.beta = (l0 == 0) ? g.beta : 1.f;
+        if (g.Sx) gp.Sx = g.Sx + l0 * g.ss_l;
+        else if (g.l_on_cols) gp.w.pc0 = g.w.pc0 + l0;
+        else gp.w.pr0 = g.w.pr0 + l0;
+        rc = launch_sketch_dense_tc_f32(gp, stream);
+        if (rc == RBX_ERR_UNSUPPORTED && l0 > 0) rc = RBX_ERR_CUDA;      // cannot happen (same shape as the first chunk); never leave C half-updated silently
+    }
+    cudaFreeAsync(ws, stream);
+    return rc;
+}
+
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
+    if (g.sx_l != 1 && g.sx_j == 1 && g.N >= 64 && g.M >= 64 && g.K >= 512 && (double) g.M * g.N * g.K >= 1e8 && !getenv("RBX_TC_NO_COPY"))
+        return tc_via_kmajor_copy(g, stream);
     if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
     if (g.M < 64 || g.N < 64 || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
     if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;

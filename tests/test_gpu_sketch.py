@@ -162,6 +162,28 @@ def test_sketch_general_dense_tensor_core_path(rb, cuda, monkeypatch):
     l0 = rb.lib.rbx_launch_count()
     assert run_dense_case(rb, cuda, "f32", "L", "C", "N", "N", 192, 256, 4096, 1.0, 0.5, prefilled=True) < 0.05
     assert rb.lib.rbx_launch_count() - l0 == 3
+    # data whose unit stride is NOT along the contraction axis (RowMajor A in a left sketch, ColMajor A in a right sketch, a
+    # transposed ColMajor A): copied chunk by chunk into a k-contiguous workspace, then the same kernels. One chunk: copy +
+    # kernel + reduce = 3 (uniform, fused) / copy + panel fill + kernel + reduce = 4 (Gaussian, three column tiles); with
+    # RBX_TC_COPY_MB = 2 the 4100 x 300 data goes in 3 chunks of 1376 rows
+    for (side, layout, opS, opA, d, n, m, alpha, beta, off, fam, ma, want, copy_mb) in [
+            ("L", "R", "N", "N", 256, 300, 4100, 1.5, -0.5, (5, 8), "U", "L", 3, None),
+            ("L", "R", "N", "N", 200, 600, 4096, 1.0, 0.0, (0, 0), "G", "L", 4, None),
+            ("R", "C", "N", "N", 256, 300, 4100, 1.0, 2.0, (0, 0), "U", "L", 3, None),
+            ("L", "C", "N", "T", 128, 512, 2052, 1.0, 0.5, (2, 4), "U", "L", 3, None),
+            ("L", "R", "N", "N", 256, 300, 4100, 1.5, -0.5, (5, 8), "U", "L", 3 * 3, "2")]:
+        if copy_mb:
+            monkeypatch.setenv("RBX_TC_COPY_MB", copy_mb)
+        l0 = rb.lib.rbx_launch_count()
+        ro, co = off
+        if side == "R":
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, m, n, alpha, beta, off=(co, ro), D_extra=(8, 3), fam=fam, ma=ma)
+        else:
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, opS, opA, d, n, m, alpha, beta, off=(ro, co), D_extra=(3, 8), fam=fam, ma=ma, lda_pad=3)
+        launches = rb.lib.rbx_launch_count() - l0
+        monkeypatch.delenv("RBX_TC_COPY_MB", raising=False)
+        assert launches == want, f"expected {want} launches (k-major copy route), saw {launches} for {(side, layout, opA, d, n, m, fam)}"
+        assert ratio < 0.05
 
 
 def test_sketch_general_dense_dmma_path(rb, cuda, monkeypatch):
