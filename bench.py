@@ -500,6 +500,8 @@ def run_extras(rb, torch, dev, hbm, pinned, args):
     S = rb.DenseSkOp(rb.DenseDist(d, m), 0)
     fl = 2.0 * d * n * m
     ms = cuda_time(torch, lambda: rb.sketch_general(L.ColMajor, O.NoTrans, O.NoTrans, d, n, m, 1.0, S, 0, 0, A, m, 0.0, B, d), 10, warm=2)
+    # the same data read as a RowMajor 65536 x 1024 matrix (unit stride along n): k-major copy route of the tcgen05 path
+    ms_r = cuda_time(torch, lambda: rb.sketch_general(L.RowMajor, O.NoTrans, O.NoTrans, d, n, m, 1.0, S, 0, 0, A, n, 0.0, B, n), 10, warm=2)
     Su = rb.DenseSkOp(rb.DenseDist(d, m, "U"), 0)
     ms_u = cuda_time(torch, lambda: rb.sketch_general(L.ColMajor, O.NoTrans, O.NoTrans, d, n, m, 1.0, Su, 0, 0, A, m, 0.0, B, d), 10, warm=2)
     peak = den["tf32_tflops"] / 3
@@ -511,6 +513,7 @@ def run_extras(rb, torch, dev, hbm, pinned, args):
                  "roofline": {"bound": "tensor", "achieved": fl / ms / 1e9, "peak": peak, "unit": "TFLOP/s", "frac": fl / ms / 1e9 / peak, "traffic": None,
                               "peak_source": "cuBLAS TF32 GEMM 8192^3 measured in this run / 3 (three MMAs per useful product)"},
                  "uniform_family": {"value": fl / ms_u / 1e6, "ms": ms_u, "frac": fl / ms_u / 1e9 / peak},
+                 "rowmajor_data": {"value": fl / ms_r / 1e6, "ms": ms_r, "frac": fl / ms_r / 1e9 / peak},
                  "e2e": {"value": fl / te / 1e9, "unit": "GFLOP/s", "ms": te * 1e3, "h2d_bytes_per_step": 4 * m * n, "d2h_bytes_per_step": 4 * d * n}}
     if cpu_on:
         out["C1"]["cpu_baseline"] = pick(cpu_c1())
