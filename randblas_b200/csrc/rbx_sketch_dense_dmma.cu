@@ -15,6 +15,9 @@
 #include "rbx_kernels.cuh"
 #include <cstdlib>
 
+#ifndef RBX_DMMA_MIN_N
+#define RBX_DMMA_MIN_N 2         // tall-skinny data: with split-K the padded 128-column tile beats the SIMT kernel
+#endif
 namespace rbx {
 
 constexpr int DM_BM = 128, DM_BN = 128, DM_BK = 16, DM_STAGES = 4, DM_THREADS = 256;
@@ -30,6 +33,10 @@ struct DmmaArgs {
     int64_t M, N, K;                         // K = panel length
     double alpha, beta;
     int tiles_n;
+    // split-K for shapes with few output tiles (tall-skinny data): CTA (tile, ks) contracts k in [ks * kper, (ks + 1) * kper) and
+    // writes its tile of partial[ks] (M x N, unit stride along C's unit-stride axis); dmma_reduce_kernel adds them in order
+    int ksplit; int64_t kper, ntiles;
+    double* partial;
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
@@ -57,9 +64,16 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp >> 2, wn = warp & 3;                 // 2 x 4 warps
     const int g = lane >> 2, t = lane & 3;
-    const int64_t i0 = ((int64_t) blockIdx.x / a.tiles_n) * BM, j0 = ((int64_t) blockIdx.x % a.tiles_n) * DM_BN;
+    const int64_t tile_id = (int64_t) blockIdx.x % a.ntiles, ks = (int64_t) blockIdx.x / a.ntiles;
+    const int64_t i0 = (tile_id / a.tiles_n) * BM, j0 = (tile_id % a.tiles_n) * DM_BN;
     const uint32_t smem_base = (uint32_t) __cvta_generic_to_shared(dm_smem);
-    const int nk = (int)((a.K + DM_BK - 1) / DM_BK);
+    // this CTA's slice of the contraction axis (the whole panel when ksplit == 1); kper is a multiple of 16, so the slice
+    // keeps the 16-byte alignment of both operands
+    const int64_t kbeg = ks * a.kper;
+    const int64_t Kc = (a.ksplit > 1) ? ((kbeg + a.kper < a.K) ? a.kper : a.K - kbeg) : a.K;
+    const double* __restrict__ Sb = a.S + kbeg;
+    const double* __restrict__ Xb = a.X + kbeg * a.sx_l;
+    const int nk = (int)((Kc + DM_BK - 1) / DM_BK);
 
     auto load_stage = [&](int kt, int slot) {
         const int64_t k0 = (int64_t) kt * DM_BK;
@@ -71,8 +85,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
             if (BM * 8 % DM_THREADS != 0 && row >= BM) break;
             const int64_t gi = i0 + row;
             const bool ok = gi < a.M;
-            const double* src = a.S + (ok ? gi : 0) * a.s_pitch + (k0 + kc < a.K ? k0 + kc : 0);
-            cp_async16(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(a.K - k0 - kc) : 0);
+            const double* src = Sb + (ok ? gi : 0) * a.s_pitch + (k0 + kc < Kc ? k0 + kc : 0);
+            cp_async16(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(Kc - k0 - kc) : 0);
         }
         if (!XJ) {
 #pragma unroll
@@ -80,16 +94,16 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
                 const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
                 const int64_t gj = j0 + row;
                 const bool ok = gj < a.N;
-                const double* src = a.X + (ok ? gj : 0) * a.sx_j + (k0 + kc < a.K ? k0 + kc : 0);
-                cp_async16(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(a.K - k0 - kc) : 0);
+                const double* src = Xb + (ok ? gj : 0) * a.sx_j + (k0 + kc < Kc ? k0 + kc : 0);
+                cp_async16(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(Kc - k0 - kc) : 0);
             }
         } else {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int c = tid + q * DM_THREADS, l = c >> 6, jc = (c & 63) * 2;
                 const int64_t gl = k0 + l;
-                const bool ok = gl < a.K;
-                const double* src = a.X + (ok ? gl : 0) * a.sx_l + (j0 + jc < a.N ? j0 + jc : 0);
+                const bool ok = gl < Kc;
+                const double* src = Xb + (ok ? gl : 0) * a.sx_l + (j0 + jc < a.N ? j0 + jc : 0);
                 cp_async16(sX + (uint32_t)(l * DM_PITCH_J + jc) * 8u, src, ok ? clamp_bytes(a.N - j0 - jc) : 0);
             }
         }
@@ -155,18 +169,21 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
     // "line" = index along the slow axis of C, "pos" = index along its unit-stride axis
     const int64_t line0 = CI ? j0 : i0, pos0 = CI ? i0 : j0;
     const int64_t nline = CI ? a.N : a.M, npos = CI ? a.M : a.N;
-    const int64_t s_line = CI ? a.sc_j : a.sc_i;
+    const bool split = a.ksplit > 1;
+    double* __restrict__ Cb = split ? a.partial + (size_t) ks * (size_t) a.M * (size_t) a.N : a.C;
+    const int64_t s_line = split ? npos : (CI ? a.sc_j : a.sc_i);
+    const double alpha = split ? 1.0 : a.alpha, beta = split ? 0.0 : a.beta;
 #pragma unroll 1
     for (int lb = warp * 16; lb < warp * 16 + 16; lb += 4) {
         double old[4][4];
-        if (a.beta != 0.0) {
+        if (beta != 0.0) {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int64_t gl = line0 + lb + u, gp = pos0 + lane + 32 * q;
                     const bool in_tile = CI ? (lane + 32 * q < BM) : (lb + u < BM);
-                    old[u][q] = (in_tile && gl < nline && gp < npos) ? a.C[gl * s_line + gp] : 0.0;
+                    old[u][q] = (in_tile && gl < nline && gp < npos) ? Cb[gl * s_line + gp] : 0.0;
                 }
         }
 #pragma unroll
@@ -176,10 +193,25 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
                 const int64_t gl = line0 + lb + u, gp = pos0 + lane + 32 * q;
                 const bool in_tile = CI ? (lane + 32 * q < BM) : (lb + u < BM);
                 if (in_tile && gl < nline && gp < npos) {
-                    const double v = a.alpha * dm_smem[(lb + u) * P + lane + 32 * q];
-                    a.C[gl * s_line + gp] = (a.beta == 0.0) ? v : v + a.beta * old[u][q];   // beta == 0: C is not read
+                    const double v = alpha * dm_smem[(lb + u) * P + lane + 32 * q];
+                    Cb[gl * s_line + gp] = (beta == 0.0) ? v : v + beta * old[u][q];   // beta == 0: C is not read
                 }
             }
+    }
+}
+
+// C = alpha * sum over ks of partial[ks] + beta * C, the splits added in increasing order (fixed => run-to-run identical);
+// partial[ks] is M x N with unit stride along C's unit-stride axis (ci: along i)
+__global__ void __launch_bounds__(256) dmma_reduce_kernel(const double* __restrict__ partial, int ksplit, int64_t M, int64_t N, bool ci,
+                                                        double alpha, double beta, double* __restrict__ C, int64_t sc_i, int64_t sc_j) {
+    const int64_t total = M * N;
+    for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t line = ci ? e / M : e / N, pos = ci ? e - line * M : e - line * N;
+        const int64_t i = ci ? pos : line, j = ci ? line : pos;
+        double sum = 0.0;
+        for (int p = 0; p < ksplit; ++p) sum += partial[(size_t) p * total + e];
+        double* c = C + i * sc_i + j * sc_j;
+        *c = (beta == 0.0) ? alpha * sum : alpha * sum + beta * (*c);
     }
 }
 
@@ -194,7 +226,7 @@ static int launch_dmma_gemm_mf(const DmmaArgs& a, int64_t tiles, cudaStream_t st
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) DM_SMEM) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_CUDA; }
         attr_set[which] = true;
     }
-    kern<<<(unsigned) tiles, DM_THREADS, DM_SMEM, stream>>>(a);
+    kern<<<(unsigned)(tiles * a.ksplit), DM_THREADS, DM_SMEM, stream>>>(a);
     count_launch();
     return check_launch("dmma_gemm_kernel");
 }
@@ -217,13 +249,35 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
     a.tiles_n = (int)((a.N + DM_BN - 1) / DM_BN);
     const int64_t tiles = (int64_t) a.tiles_n * ((a.M + 16 * mf - 1) / (16 * mf));
     if (tiles > 0x7fffffffll) return RBX_ERR_UNSUPPORTED;
-    return mf == 8 ? launch_dmma_gemm_mf<8>(a, tiles, stream) : mf == 7 ? launch_dmma_gemm_mf<7>(a, tiles, stream)
-                                                                      : launch_dmma_gemm_mf<6>(a, tiles, stream);
+    // few output tiles (tall-skinny data: M x N small, K long): split the contraction axis so that about two waves of CTAs run
+    int64_t ksplit = (2 * kNumSMs) / tiles;
+    const int64_t nk = (a.K + DM_BK - 1) / DM_BK;
+    if (ksplit > nk / 16) ksplit = nk / 16;                   // at least 16 k-tiles (256 contraction indices) per split
+    if (ksplit < 1) ksplit = 1;
+    if (const char* ev = getenv("RBX_DMMA_KSPLIT")) { const int64_t v = atoll(ev); if (v >= 1 && v <= nk) ksplit = v; }
+    a.ntiles = tiles; a.ksplit = (int) ksplit; a.partial = nullptr;
+    a.kper = ((nk + ksplit - 1) / ksplit) * DM_BK;
+    a.ksplit = (int)((a.K + a.kper - 1) / a.kper);            // no empty splits
+    if (a.ksplit > 1 && ws_alloc(&a.partial, sizeof(double) * (size_t) a.ksplit * (size_t) a.M * (size_t) a.N, stream) != cudaSuccess) {
+        cudaGetLastError();
+        return RBX_ERR_ALLOC;
+    }
+    int rc = mf == 8 ? launch_dmma_gemm_mf<8>(a, tiles, stream) : mf == 7 ? launch_dmma_gemm_mf<7>(a, tiles, stream)
+                                                                        : launch_dmma_gemm_mf<6>(a, tiles, stream);
+    if (rc == RBX_OK && a.ksplit > 1) {
+        int64_t blocks = (a.M * a.N + 255) / 256;
+        if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+        dmma_reduce_kernel<<<(unsigned) blocks, 256, 0, stream>>>(a.partial, a.ksplit, a.M, a.N, a.sc_i == 1, a.alpha, a.beta, a.C, a.sc_i, a.sc_j);
+        count_launch();
+        rc = check_launch("dmma_reduce_kernel");
+    }
+    if (a.partial) cudaFreeAsync(a.partial, stream);
+    return rc;
 }
 
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 64 || g.N < 64 || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 64 || g.N < RBX_DMMA_MIN_N || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
     if (reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
     if (!((g.sx_l == 1 && g.sx_j % 2 == 0) || (g.sx_j == 1 && g.sx_l % 2 == 0))) return RBX_ERR_UNSUPPORTED;
     if (g.Sx && (g.ss_l != 1 || g.ss_i % 2 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0)) return RBX_ERR_UNSUPPORTED;
