@@ -277,7 +277,7 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
 
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 64 || g.N < RBX_DMMA_MIN_N || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 1 || g.N < RBX_DMMA_MIN_N || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
     if (reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
     if (!((g.sx_l == 1 && g.sx_j % 2 == 0) || (g.sx_j == 1 && g.sx_l % 2 == 0))) return RBX_ERR_UNSUPPORTED;
     if (g.Sx && (g.ss_l != 1 || g.ss_i % 2 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0)) return RBX_ERR_UNSUPPORTED;

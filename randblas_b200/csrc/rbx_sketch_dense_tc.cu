@@ -460,10 +460,10 @@ static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream)
 
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.sx_l != 1 && g.sx_j == 1 && g.N >= RBX_TC_MIN_N && g.M >= 64 && g.K >= 512 && (double) g.M * g.N * g.K >= 1e8 && !getenv("RBX_TC_NO_COPY"))
+    if (g.sx_l != 1 && g.sx_j == 1 && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= 512 && (double) g.M * g.N * g.K >= 1e8 && !getenv("RBX_TC_NO_COPY"))
         return tc_via_kmajor_copy(g, stream);
     if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 64 || g.N < RBX_TC_MIN_N || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 1 || g.N < RBX_TC_MIN_N || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
     if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;
     if (g.alpha == 0.f) return launch_scale_view<float>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
     if (g.Sx) {      // DenseSkOp::buff given: k-contiguous rows, 16-byte aligned, no ragged float4 at the end of a row

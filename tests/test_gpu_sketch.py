@@ -225,6 +225,11 @@ def test_sketch_general_dense_dmma_path(rb, cuda, monkeypatch):
             assert run_dense_case(rb, cuda, dt, "L", layout, "N", "N", d, n, m, 1.5, -0.5, fam="G" if n != 17 else "U", lda_pad=0 if layout == "C" else 3) < 0.05
             got = rb.lib.rbx_launch_count() - l0
             assert got >= 2 and got != 1, (dt, layout, d, n, m, got)
+        # a small sketch dimension (d = 1 .. 48): the operator tile is mostly padding, the data still streams through the tensor-core kernels
+        for (layout, d, n, m) in (("C", 5, 300, 100000), ("R", 33, 200, 30000), ("C", 1, 1000, 150000)):
+            l0 = rb.lib.rbx_launch_count()
+            assert run_dense_case(rb, cuda, dt, "L", layout, "N", "N", d, n, m, 1.0, 0.0, fam="G", off=(0, 4), D_extra=(2, 8)) < 0.05
+            assert rb.lib.rbx_launch_count() - l0 >= 2, (dt, layout, d, n, m)
 
 
 def test_nan_in_B_is_overwritten_when_beta_is_zero(rb, cuda):
