@@ -423,6 +423,14 @@ __global__ void __launch_bounds__(256) tc_kmajor_copy_kernel(const float* __rest
     }
 }
 
+// dst[j * pitch + l] = X[l + j * sx_j]: k-contiguous data whose base or leading dimension is not 16-byte aligned, repacked
+__global__ void __launch_bounds__(256) tc_repack_kernel(const float* __restrict__ src, int64_t kl, int64_t N, int64_t sx_j,
+                                                        float* __restrict__ dst, int64_t pitch) {
+    const int64_t j = blockIdx.y;
+    for (int64_t l = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; l < kl; l += (int64_t) gridDim.x * blockDim.x)
+        dst[j * pitch + l] = __ldcs(src + l + j * sx_j);
+}
+
 // Data with unit stride along j instead of along the contraction axis (e.g. RowMajor A in a left sketch, ColMajor A in a
 // right sketch): the tcgen05 kernel wants K-major tiles, so the data is copied chunk by chunk along k into a k-contiguous
 // workspace (at most 512 MB, whatever K is) and every chunk takes the normal path with the operator window advanced and
@@ -440,8 +448,13 @@ static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream)
     int rc = RBX_OK;
     for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kc) {
         const int64_t kl = (l0 + kc <= g.K) ? kc : g.K - l0;
-        dim3 grid((unsigned)((kl + 63) / 64), (unsigned)((g.N + 63) / 64));
-        tc_kmajor_copy_kernel<<<grid, 256, 0, stream>>>(g.X + l0 * g.sx_l, kl, g.N, g.sx_l, ws, kc);
+        if (g.sx_l == 1) {                    // k-contiguous but misaligned: plain repack
+            int64_t bx = (kl + 255) / 256; if (bx > 64) bx = 64;
+            tc_repack_kernel<<<dim3((unsigned) bx, (unsigned) g.N), 256, 0, stream>>>(g.X + l0, kl, g.N, g.sx_j, ws, kc);
+        } else {
+            dim3 grid((unsigned)((kl + 63) / 64), (unsigned)((g.N + 63) / 64));
+            tc_kmajor_copy_kernel<<<grid, 256, 0, stream>>>(g.X + l0 * g.sx_l, kl, g.N, g.sx_l, ws, kc);
+        }
         count_launch();
         rc = check_launch("tc_kmajor_copy_kernel");
         if (rc != RBX_OK) break;
@@ -460,7 +473,10 @@ static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream)
 
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.sx_l != 1 && g.sx_j == 1 && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= 512 && (double) g.M * g.N * g.K >= 1e8 && !getenv("RBX_TC_NO_COPY"))
+    const bool j_major = g.sx_l != 1 && g.sx_j == 1;
+    const bool k_major_misaligned = g.sx_l == 1 && g.N >= 2 && g.N <= 65535 && ((g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0);
+    if ((j_major || k_major_misaligned) && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= 512 && (double) g.M * g.N * g.K >= 1e8 &&
+        !getenv("RBX_TC_NO_COPY"))
         return tc_via_kmajor_copy(g, stream);
     if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
     if (g.M < 1 || g.N < RBX_TC_MIN_N || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;

@@ -171,7 +171,8 @@ def test_sketch_general_dense_tensor_core_path(rb, cuda, monkeypatch):
             ("L", "R", "N", "N", 200, 600, 4096, 1.0, 0.0, (0, 0), "G", "L", 4, None),
             ("R", "C", "N", "N", 256, 300, 4100, 1.0, 2.0, (0, 0), "U", "L", 3, None),
             ("L", "C", "N", "T", 128, 512, 2052, 1.0, 0.5, (2, 4), "U", "L", 3, None),
-            ("L", "R", "N", "N", 256, 300, 4100, 1.5, -0.5, (5, 8), "U", "L", 3 * 3, "2")]:
+            ("L", "R", "N", "N", 256, 300, 4100, 1.5, -0.5, (5, 8), "U", "L", 3 * 3, "2"),
+            ("L", "C", "N", "N", 256, 300, 4100, 1.0, 0.0, (0, 0), "U", "L", 3, None)]:      # k-contiguous but lda = 4103 is not a multiple of 4: repacked
         if copy_mb:
             monkeypatch.setenv("RBX_TC_COPY_MB", copy_mb)
         l0 = rb.lib.rbx_launch_count()
