@@ -646,7 +646,10 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     if (!cols_contig && sx_j != 1) return RBX_ERR_UNSUPPORTED;
     if (vec_nnz > 32 || M > SASO_MAX_RB * SASO_R || M < 1 || N < 1 || K < 64) return RBX_ERR_UNSUPPORTED;
     const int64_t ld = cols_contig ? sx_j : sx_l;
-    if (reinterpret_cast<uintptr_t>(X) % 16 != 0 || (ld * (int64_t) sizeof(T)) % 16 != 0) return RBX_ERR_UNSUPPORTED;
+    // row-contiguous data is staged with 16-byte cp.async (base and leading dimension 16-byte aligned); column-contiguous
+    // data goes element by element (8 / 4-byte cp.async) and needs nothing beyond the natural alignment of T
+    if (!cols_contig && (reinterpret_cast<uintptr_t>(X) % 16 != 0 || (ld * (int64_t) sizeof(T)) % 16 != 0)) return RBX_ERR_UNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(X) % sizeof(T) != 0) return RBX_ERR_UNSUPPORTED;
     if (K > (int64_t) 0x7fffffff - 512 || N > 0x7fffffff) return RBX_ERR_UNSUPPORTED;
     if (alpha == (T) 0) return launch_scale_view<T>(C, M, N, sc_i, sc_j, beta, stream);
 
