@@ -438,6 +438,39 @@ def test_general_sparse_operator_path_is_deterministic(rb, cuda, dt):
 
 
 @pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_general_sparse_operator_path_relays_out_column_contiguous_data(rb, cuda, dt, monkeypatch):
+    """column-contiguous data with >= 128 columns on the general path (LASO, vec_nnz > 32, explicit triplets): blocks of columns
+    are re-laid with contiguous rows into a workspace and gathered with the row kernel (one extra launch per block, visible in
+    the launch count), in one block and -- with RBX_CG_RELAYOUT_MB = 24 -- in several (identical bits), and the same values as
+    without the re-layout to rounding; ragged column counts and a padded leading dimension included"""
+    npdt = np.float32 if dt == "f32" else np.float64
+    rng = np.random.default_rng(2)
+    for (d, n, m, k, ma, lda_pad) in [(24, 300, 20000, 600, "L", 0), (64, 130, 6000, 40, "S", 3), (20, 257, 3000, 300, "L", 1)]:
+        run_sparseop_case(rb, cuda, dt, "L", "C", "N", "N", d, n, m, 1.5, -0.5, k, ma, key=5, lda_pad=lda_pad)
+        A = torch.from_numpy(rng.standard_normal((m + lda_pad) * n).astype(npdt)).to(cuda)
+        S = rb.SparseSkOp(rb.SparseDist(d, m, k, ma), 11, dtype=TDT[dt])
+        outs, launches = [], []
+        for mode in ("default", "blocks", "off"):
+            monkeypatch.delenv("RBX_CG_RELAYOUT_MB", raising=False); monkeypatch.delenv("RBX_CG_NO_RELAYOUT", raising=False)
+            if mode == "blocks":
+                monkeypatch.setenv("RBX_CG_RELAYOUT_MB", "24")
+            if mode == "off":
+                monkeypatch.setenv("RBX_CG_NO_RELAYOUT", "1")
+            B = torch.full((d * n,), 0.25, dtype=TDT[dt], device=cuda)
+            l0 = rb.lib.rbx_launch_count()
+            rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 2.0, S, 0, 0, A, m + lda_pad, 0.5, B, d)
+            launches.append(rb.lib.rbx_launch_count() - l0)
+            outs.append(B)
+        monkeypatch.delenv("RBX_CG_RELAYOUT_MB", raising=False); monkeypatch.delenv("RBX_CG_NO_RELAYOUT", raising=False)
+        # one block or several: the same row kernel, the same order of additions -> identical bits; the 4-column kernel of the
+        # route without re-layout folds its lanes' partial sums by a butterfly, i.e. another (equally fixed) order
+        assert torch.equal(outs[0], outs[1]), (d, n, m, k, ma)
+        tol = 1e-4 if dt == "f32" else 1e-12
+        assert torch.allclose(outs[0], outs[2], rtol=tol, atol=tol * float(outs[2].abs().max())), (d, n, m, k, ma)
+        assert launches[0] == launches[2] + 1 and launches[1] >= launches[0], (launches, d, n, m)
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_saso_windows_up_to_8192_rows_take_the_streaming_kernel(rb, cuda, dt):
     """operator windows of 4097..8192 rows (5 to 8 row blocks of the tile kernel): same result as the definition, and the launch
     count shows the streaming kernel ran (prep + two tile variants [+ reduce]), not fill_sparse + regroup + gather"""
