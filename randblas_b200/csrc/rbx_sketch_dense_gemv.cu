@@ -40,6 +40,30 @@ __global__ void __launch_bounds__(256) gemv_rows_kernel(const GvArgs a, const T*
     const int64_t cb0 = (a.w.pc0 + l_begin) >> 2;                         // first counter column touched
     const int64_t row_ctr = (a.w.pr0 + i) * a.w.W;
     T acc = (T) 0;
+    // interior chunks of an aligned window with a unit-stride, 16-byte aligned x (the usual call): no per-element bounds, x read
+    // four elements at a time, the counter a running 64-bit sum (its high half is constant unless the low half wraps here)
+    const Ctr128 c0 = ctr_add(a.w.ctr, (uint64_t)(row_ctr + cb0 + lane));
+    const uint64_t c0_lo = ((uint64_t) c0.v[1] << 32) | c0.v[0];
+    if ((a.w.pc0 & 3) == 0 && a.sx == 1 && l_begin + GV_LC <= a.K && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && c0_lo + 32ull * GV_U >= c0_lo) {
+        const T* xp = x + l_begin + 4 * lane;
+#pragma unroll 2
+        for (int u = 0; u < GV_U; ++u) {
+            const uint64_t lo = c0_lo + 32ull * u;
+            const float4 v = generate4<FAMILY>(philox4x32_10((uint32_t) lo, (uint32_t)(lo >> 32), c0.v[2], c0.v[3], a.w.key.v[0], a.w.key.v[1]), tab);
+            T xv[4];
+            if (sizeof(T) == 4) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(xp + 128 * u));
+                xv[0] = (T) t.x; xv[1] = (T) t.y; xv[2] = (T) t.z; xv[3] = (T) t.w;
+            } else {
+                const double2 t0 = __ldg(reinterpret_cast<const double2*>(xp + 128 * u)), t1 = __ldg(reinterpret_cast<const double2*>(xp + 128 * u) + 1);
+                xv[0] = (T) t0.x; xv[1] = (T) t0.y; xv[2] = (T) t1.x; xv[3] = (T) t1.y;
+            }
+            acc = fma(gv_value<T>(v.x, FAMILY == 'U'), xv[0], acc);
+            acc = fma(gv_value<T>(v.y, FAMILY == 'U'), xv[1], acc);
+            acc = fma(gv_value<T>(v.z, FAMILY == 'U'), xv[2], acc);
+            acc = fma(gv_value<T>(v.w, FAMILY == 'U'), xv[3], acc);
+        }
+    } else
 #pragma unroll 2
     for (int u = 0; u <= GV_U; ++u) {                                     // one extra counter when pc0 is not a multiple of 4
         const int64_t cb = cb0 + lane + 32 * u;
