@@ -44,7 +44,7 @@ int rbx_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* st
 int rbx_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream);
 int rbx_stream_synchronize(void* stream);
 /* Kernel workspaces (operator codes, split partials, operator slabs) come from a private stream-ordered pool per device
-   (never the default pool the application shares) that keeps up to 1/32 of the device's memory mapped between calls
+   (never the default pool the application shares) that keeps up to 1/8 of the device's memory mapped between calls (only what calls really used; re-mapping the 12 GB of a full-size sketch_sparse costs more than the call)
    (RBX_WS_KEEP_MB overrides); this synchronises the device and returns all of it to the driver. */
 int rbx_trim_workspace(void);
 /* bytes of the current device's private workspace pool: in use now, the most in use at any time since the last reset (the

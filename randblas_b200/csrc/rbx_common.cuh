@@ -22,8 +22,8 @@ inline int check_launch(const char* what) {
 }
 // Stream-ordered workspaces come from a PRIVATE memory pool per device (cudaMemPoolCreate), not from the device's default
 // pool that the host application and other libraries (torch's allocator, cuBLAS) share: nothing this library does changes
-// their pool's behaviour. The private pool keeps up to a bounded amount mapped between calls (release threshold = 1/32 of
-// the device's memory, 5.6 GiB on a B200; RBX_WS_KEEP_MB overrides) -- a workspace freed by one call is still mapped for the
+// their pool's behaviour. The private pool keeps up to a bounded amount mapped between calls (release threshold = 1/8 of
+// the device's memory, 22 GiB on a B200, and only ever what a call really used; RBX_WS_KEEP_MB overrides) -- a workspace freed by one call is still mapped for the
 // next, because re-mapping a few hundred MB costs more than the kernels here -- and hands anything above that back to the
 // driver at the next synchronisation. rbx_trim_workspace() returns all of it. Creation is guarded by std::call_once.
 struct WsState {
@@ -45,7 +45,7 @@ inline cudaMemPool_t ws_pool(int dev) {
         if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) { cudaGetLastError(); return; }
         size_t free_b = 0, total_b = 0;
         unsigned long long keep = 4ull << 30;
-        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) keep = (unsigned long long) total_b / 32; else cudaGetLastError();
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) keep = (unsigned long long) total_b / 8; else cudaGetLastError();
         if (const char* ev = getenv("RBX_WS_KEEP_MB")) keep = (unsigned long long) atoll(ev) << 20;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
         S.pool[dev] = pool;
