@@ -855,6 +855,14 @@ int rbx_host_sketch_dense_##SUF(char side, char layout, char opS, char opA, int6
                                 T* B_host, int64_t ldb) {                                                                         \
     int64_t rA, cA, rB, cB;                                                                                                       \
     host_dims(side, opA, p0, p1, p2, &rA, &cA, &rB, &cB);                                                                         \
+    if (use_slabs<T>(side, opS, opA, p1, p2)) {      /* >= 1 GiB of data: slab i + 1 crosses PCIe while slab i is sketched */     \
+        { DryRun dry; RBX_TRY(sketch_dense<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, \
+                                              key, nullptr, 'C', ro_s, co_s, (const T*) nullptr, lda, beta, (T*) nullptr, ldb, nullptr)); } \
+        return staged_left_slabs<T>(layout, p0, p1, p2, A_host, lda, beta, B_host, ldb,                                           \
+            [&](int64_t k0, int64_t kl, const T* A_slab, int64_t lda_slab, T beta_eff, T* B_dev, void* st) {                      \
+                return sketch_dense<T>(side, layout, opS, opA, p0, p1, kl, alpha, D_rows, D_cols, family, major_axis, ctr, key,   \
+                                       nullptr, 'C', ro_s, co_s + k0, A_slab, lda_slab, beta_eff, B_dev, ldb, st); });            \
+    }                                                                                                                             \
     return with_staged<T>(layout, rA, cA, A_host, lda, rB, cB, B_host, ldb, beta != (T) 0,                                        \
         [&](const T* A_dev, T* B_dev, void* st) {                                                                                 \
             return sketch_dense<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key,       \

@@ -811,6 +811,14 @@ def test_host_pointer_pipelined_slabs(rb, cuda, layout):
     rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.5, S, 0, 24, A.cpu(), lda, -0.5, Bh, ldb)
     scale = float(Bd.abs().max())
     assert float((Bh - Bd.cpu()).abs().max()) <= 1e-12 * scale
+    # the same pipeline serves dense operators (co_s advanced per slab selects the operator's columns of that slab)
+    Sd = rb.DenseSkOp(rb.DenseDist(d, m + 24), 5, dtype=torch.float64)
+    Bd = B0.to(cuda)
+    rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.5, Sd, 0, 24, A, lda, -0.5, Bd, ldb)
+    Bh = B0.clone()
+    rb.sketch_general(rb.Layout(layout), rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.5, Sd, 0, 24, A.cpu(), lda, -0.5, Bh, ldb)
+    scale = float(Bd.abs().max())
+    assert float((Bh - Bd.cpu()).abs().max()) <= 1e-11 * scale
 
 
 def test_implicit_dense_sketch_allocates_nothing_proportional_to_the_operator(rb, cuda):
