@@ -136,7 +136,7 @@ __device__ __forceinline__ void block_excl_scan(const uint32_t* in, uint32_t* ou
 //        tail of the distribution), read straight from global memory; ws[chunk * ws_stride + b] = their start.
 template <int KMAX, int HALVES>
 __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key64 key, int vec_nnz, int64_t dim_major, int64_t ro, int64_t co,
-                                                               int64_t M, int64_t K, int CK, int nbuckets, int nrb, int cols_contig, int cap,
+                                                               int64_t M, int64_t K, int CK, int nbuckets, int nrb, int cols_contig, int cap, int R,
                                                                uint32_t* __restrict__ stream, int stream_stride,
                                                                uint32_t* __restrict__ rec, int rec_stride,
                                                                uint32_t* __restrict__ ws, int ws_stride, int* __restrict__ spill_flag) {
@@ -168,8 +168,9 @@ __global__ void __launch_bounds__(SASO_THREADS) saso_prep_kernel(Ctr128 ctr, Key
         if (l >= K) break;
         const uint32_t base = (uint32_t) cc * pitch_el;
         fy_vector<KMAX>(ctr, key, co + l, vec_nnz, dim_major, [&](int j, int64_t idx, bool negative) {
-            const int64_t r = idx - ro;
+            int64_t r = idx - ro;
             if (r >= 0 && r < M) {
+                r += (int64_t)(cc % R) * M;      // R > 1: column cc of the chunk feeds copy (cc mod R) of the M output rows (see launch_saso_fast)
                 tcode[cc * vec_nnz + j] = base | (negative ? SASO_SIGN : 0u);
                 trow[cc * vec_nnz + j] = (uint16_t) r;
                 atomicAdd(&rowcnt[r], 1u);
@@ -258,7 +259,8 @@ struct SasoArgs {
     int stream_stride, rec_stride, ws_stride;
     int CK, cap;                                       // rows per chunk; tail elements a row block's region holds
     int nbuckets, njb, nrb, msplit, nchunks, dbg_skip;
-    int64_t M;
+    int direct;                                        // 1: one split and no row copies -> the tile kernel stores alpha * acc + beta * C itself
+    int64_t M;                                         // rows the tile kernel owns (R copies of the window's rows when R > 1)
     T alpha, beta;
     T* C; int64_t sc_i, sc_j;
     T* partial;                                        // [msplit][M][njb * W] when msplit > 1
@@ -597,7 +599,7 @@ __global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const S
         for (int s = 0; s < NS; ++s) {
             const int64_t row = (int64_t) bucket * SASO_RW + sub * NS + s;
             if (row < a.M && col < a.N) {
-                if (a.msplit == 1) {
+                if (a.direct) {
                     T* c = a.C + row * a.sc_i + col * a.sc_j;
                     *c = (a.beta == (T) 0) ? a.alpha * acc[s] : a.alpha * acc[s] + a.beta * (*c);
                 } else {
@@ -653,7 +655,14 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     if (K > (int64_t) 0x7fffffff - 512 || N > 0x7fffffff) return RBX_ERR_UNSUPPORTED;
     if (alpha == (T) 0) return launch_scale_view<T>(C, M, N, sc_i, sc_j, beta, stream);
 
-    const int nbuckets = (int)((M + SASO_RW - 1) / SASO_RW);
+    // A CTA's 16 consumer warps own 64 rows each. A window of few rows would leave most of them idle and pile every chunk's
+    // entries onto few accumulator slots (three per record, the rest in serial tails): d = 64 ran 14x slower than d = 1024 for
+    // the same number of updates. Such windows are therefore replicated: R copies of the M rows, column cc of a chunk feeding
+    // copy (cc mod R), so that the tile kernel sees Mv = R * M <= 1024 rows with 1 / R of the entries each; the copies are
+    // summed by the reduce kernel together with the contraction splits (a fixed order: still bitwise reproducible).
+    const int R = (M <= SASO_R / 2 && !getenv("RBX_SASO_NO_REPL")) ? (int)(SASO_R / M) : 1;
+    const int64_t Mv = M * R;
+    const int nbuckets = (int)((Mv + SASO_RW - 1) / SASO_RW);
     const int nrb = (nbuckets + SASO_WARPS - 1) / SASO_WARPS;           // row blocks of 1024 rows
     const int njb = (int)((N + W - 1) / W);
     // rows of A per chunk: as many as the ring stages (A chunk + the records and tails that go with it) fit in shared memory
@@ -664,7 +673,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         if ((size_t) ck * vec_nnz * 10 + (size_t)(2 * nbuckets * SASO_RW + 3 * nbuckets * NS + 2) * 4 + 16 > SMEM_MAX) continue;   // the prep kernel's sort
         // tail elements of one row block per chunk: mean + 8 sigma (Poisson tails; sigma^2 < 2 * mean); a bucket that
         // does not fit reads its tails from global memory
-        const double lambda = (double) ck * (double) vec_nnz / (double) S_rows;
+        const double lambda = (double) ck * (double) vec_nnz / ((double) S_rows * R);
         const double mean_rb = saso_mean_tail(lambda, HALVES) * SASO_WARPS * NS;
         int c = ((int)(mean_rb + 8.0 * sqrt(2.0 * mean_rb + 1.0)) + 32 + 31) & ~31;
         if (const char* ev = getenv("RBX_SASO_CAP")) { const int v = atoi(ev); if (v >= 0) c = (v + 31) & ~31; }    // tests: force the spill path
@@ -688,7 +697,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     const int ws_stride = (nbuckets + 1 + 3) & ~3;
     uint32_t* codes = nullptr; uint32_t* rec = nullptr; uint32_t* ws = nullptr; T* partial = nullptr; int* flag = nullptr;
     const size_t Np = (size_t) njb * W;
-    const size_t part_bytes = msplit > 1 ? (size_t) msplit * M * Np * sizeof(T) : 0;
+    const bool direct = (msplit == 1 && R == 1);
+    const size_t part_bytes = direct ? 0 : (size_t) msplit * Mv * Np * sizeof(T);
     if (ws_alloc(&codes, (size_t) nchunks * stream_stride * 4, stream) != cudaSuccess ||
         ws_alloc(&rec, (size_t) nchunks * rec_stride * 4, stream) != cudaSuccess ||
         ws_alloc(&ws, (size_t) nchunks * ws_stride * 4, stream) != cudaSuccess ||
@@ -706,7 +716,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     if (rc == RBX_OK) {
         auto kern = vec_nnz <= 8 ? saso_prep_kernel<8, HALVES> : saso_prep_kernel<32, HALVES>;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) prep_smem);
-        kern<<<nchunks, SASO_THREADS, prep_smem, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, CK, nbuckets, nrb, cols_contig ? 1 : 0, cap,
+        kern<<<nchunks, SASO_THREADS, prep_smem, stream>>>(ctr, key, (int) vec_nnz, S_rows, ro, co, M, K, CK, nbuckets, nrb, cols_contig ? 1 : 0, cap, R,
                                                            codes, stream_stride, rec, rec_stride, ws, ws_stride, flag);
         count_launch();
         rc = check_launch("saso_prep_kernel");
@@ -719,7 +729,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         a.CK = CK; a.cap = cap;
         a.nbuckets = nbuckets; a.njb = njb; a.nrb = nrb; a.msplit = msplit; a.nchunks = nchunks;
         a.dbg_skip = getenv("RBX_SASO_SKIP") ? atoi(getenv("RBX_SASO_SKIP")) : 0;
-        a.M = M; a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial; a.spill_flag = flag;
+        a.M = Mv; a.direct = direct ? 1 : 0;
+        a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial; a.spill_flag = flag;
         const unsigned grid = (unsigned)(njb * msplit * nrb);
         const size_t smem = nst * stage;
         auto tile = cols_contig ? saso_tile_kernel<T, true, false> : saso_tile_kernel<T, false, false>;
@@ -730,10 +741,11 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         tile_spill<<<grid, SASO_TILE_THREADS, smem, stream>>>(a);      // returns at once unless the prep kernel raised the flag
         count_launch(); count_launch();
         rc = check_launch("saso_tile_kernel");
-        if (rc == RBX_OK && msplit > 1) {
+        if (rc == RBX_OK && !direct) {
             int64_t blocks = (M * N + 255) / 256;
             if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-            saso_reduce_kernel<T><<<(unsigned) blocks, 256, 0, stream>>>(partial, msplit, M, N, (int64_t) Np, alpha, beta, C, sc_i, sc_j);
+            // partial[(ms * Mv + g * M + row) * Np + col] = part (ms * R + g) of M rows: msplit * R parts, added in that order
+            saso_reduce_kernel<T><<<(unsigned) blocks, 256, 0, stream>>>(partial, msplit * R, M, N, (int64_t) Np, alpha, beta, C, sc_i, sc_j);
             count_launch();
             rc = check_launch("saso_reduce_kernel");
         }

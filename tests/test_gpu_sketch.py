@@ -335,6 +335,32 @@ def test_saso_medium(rb, cuda, dt):
 
 
 @pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_saso_small_windows_are_replicated(rb, cuda, dt, monkeypatch):
+    """windows of at most 512 rows run the streaming kernel on R = 1024 // M copies of their rows (column cc of a chunk feeds copy
+    cc mod R), summed by the reduce kernel: right against the oracle for M that do and do not divide 1024, with offsets and
+    beta, equal to the unreplicated run to rounding, and bit-identical from run to run"""
+    for layout in "CR":
+        for (d, n, m, off, extra) in [(16, 50, 9000, (0, 0), (0, 0)), (100, 33, 12000, (3, 500), (7, 900)), (300, 64, 5000, (0, 0), (0, 0)), (512, 40, 4096, (0, 0), (0, 0))]:
+            run_sparseop_case(rb, cuda, dt, "L", layout, "N", "N", d, n, m, 1.5, -0.5, 8, "S", key=21, off=off, D_extra=extra)
+    npdt = np.float32 if dt == "f32" else np.float64
+    rng = np.random.default_rng(3)
+    d, n, m = 48, 96, 20000
+    A = torch.from_numpy(rng.standard_normal(m * n).astype(npdt)).to(cuda)
+    S = rb.SparseSkOp(rb.SparseDist(d, m, 8), 5, dtype=TDT[dt])
+    outs = []
+    for mode in ("repl", "repl", "norepl"):
+        if mode == "norepl":
+            monkeypatch.setenv("RBX_SASO_NO_REPL", "1")
+        B = torch.zeros(d * n, dtype=TDT[dt], device=cuda)
+        rb.sketch_general(rb.Layout.ColMajor, rb.Op.NoTrans, rb.Op.NoTrans, d, n, m, 1.0, S, 0, 0, A, m, 0.0, B, d)
+        outs.append(B)
+    monkeypatch.delenv("RBX_SASO_NO_REPL", raising=False)
+    assert torch.equal(outs[0], outs[1])
+    tol = 1e-4 if dt == "f32" else 1e-12
+    assert torch.allclose(outs[0], outs[2], rtol=tol, atol=tol * float(outs[2].abs().max()))
+
+
+@pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_saso_tail_paths(rb, cuda, dt, monkeypatch):
     """The streaming SASO kernel's three homes of an entry: the slot record (first three per row and chunk), the staged
     tail region, and -- when a bucket's tails do not fit the region -- global memory. RBX_SASO_CAP shrinks the region so
