@@ -127,7 +127,8 @@ int launch_sketch_dense_gemv(const GemmOperands<T>& g, cudaStream_t stream) {
     GvArgs a;
     a.w = g.w; a.M = g.M; a.K = g.K; a.sx = g.sx_l;
     a.nchunks = g.l_on_cols ? (g.K + GV_LC - 1) / GV_LC : (g.K + GV_ROWS - 1) / GV_ROWS;
-    if (a.nchunks > 65535 || (g.M + 7) / 8 > 65535) return RBX_ERR_UNSUPPORTED;
+    // grid.y limits: the row kernel puts row blocks there, the column kernel the chunks
+    if (g.l_on_cols ? ((g.M + 7) / 8 > 65535 || a.nchunks > 0x7fffffffll) : (a.nchunks > 65535)) return RBX_ERR_UNSUPPORTED;
     T* partial = nullptr;
     if (ws_alloc(&partial, sizeof(T) * (size_t) a.nchunks * (size_t) g.M, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
     const bool G = g.w.family == 'G';
