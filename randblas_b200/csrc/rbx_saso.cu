@@ -644,7 +644,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     constexpr int NS = SASO_RW / HALVES;
     constexpr size_t SMEM_MAX = 227 * 1024;
     // envelope of this kernel; everything else goes to the general path
-    const bool cols_contig = (sx_l == 1 && sx_j != 1);
+    const bool cols_contig = (sx_l == 1 && (sx_j != 1 || N == 1));      // a single column is column-contiguous whatever its leading dimension says
     if (!cols_contig && sx_j != 1) return RBX_ERR_UNSUPPORTED;
     if (vec_nnz > 32 || M > SASO_MAX_RB * SASO_R || M < 1 || N < 1 || K < 64) return RBX_ERR_UNSUPPORTED;
     const int64_t ld = cols_contig ? sx_j : sx_l;
