@@ -20,6 +20,13 @@ inline int check_launch(const char* what) {
     }
     return RBX_OK;
 }
+// Work threshold (multiply-adds) below which the dense sketch takes the one-launch SIMT kernel instead of the tensor-core
+// kernels. RBX_DENSE_MIN_MACS overrides it: the randomized parity tests set it to 0 so that small ragged shapes reach the
+// tensor-core kernels too.
+inline double dense_min_macs(double dflt) {
+    const char* ev = getenv("RBX_DENSE_MIN_MACS");
+    return ev ? atof(ev) : dflt;
+}
 // Stream-ordered workspaces come from a PRIVATE memory pool per device (cudaMemPoolCreate), not from the device's default
 // pool that the host application and other libraries (torch's allocator, cuBLAS) share: nothing this library does changes
 // their pool's behaviour. The private pool keeps up to a bounded amount mapped between calls (release threshold = 1/8 of

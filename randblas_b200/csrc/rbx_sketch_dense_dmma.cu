@@ -10,9 +10,11 @@
 //
 // dmma_gemm_kernel: C (M x N) = alpha * Sp (M x Kp, k contiguous) * X (Kp x N) + beta * C.
 //   CTA tile 128 x 128 x 16, 8 warps as 2 (M) x 4 (N), warp tile 64 x 32 = 8 x 4 DMMA.8x8x4 fragments (64 accumulators
-//   per thread). Operands come through a 4-stage cp.async ring (16-byte chunks, zero-fill for ragged edges); rows are
-//   padded so that the 8-byte fragment loads of a half-warp hit 16 distinct bank pairs.
+//   per thread). Operands come through a 4-stage cp.async ring (16-byte chunks, zero-fill for ragged edges; 8-byte chunks
+//   for an operand whose base or leading dimension is not 16-byte aligned); rows are padded so that the 8-byte fragment
+//   loads of a half-warp hit 16 distinct bank pairs.
 #include "rbx_kernels.cuh"
+#include "rbx_copy.cuh"
 #include <cstdlib>
 
 #ifndef RBX_DMMA_MIN_N
@@ -37,12 +39,18 @@ struct DmmaArgs {
     // writes its tile of partial[ks] (M x N, unit stride along C's unit-stride axis); dmma_reduce_kernel adds them in order
     int ksplit; int64_t kper, ntiles;
     double* partial;
+    // 16-byte copies need a 16-byte aligned base and an even pitch; an operand without them (an odd leading dimension) is
+    // staged with 8-byte copies instead: twice the copy instructions, the same DMMA stream
+    int s16, x16;
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src, int src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
@@ -79,32 +87,59 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         const int64_t k0 = (int64_t) kt * DM_BK;
         const uint32_t sS = smem_base + (uint32_t)(slot * 2 * DM_TILE_DOUBLES) * 8u;
         const uint32_t sX = sS + (uint32_t) DM_TILE_DOUBLES * 8u;
+        if (a.s16) {
 #pragma unroll
-        for (int q = 0; q < (BM * 8 + DM_THREADS - 1) / DM_THREADS; ++q) {
-            const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
-            if (BM * 8 % DM_THREADS != 0 && row >= BM) break;
-            const int64_t gi = i0 + row;
-            const bool ok = gi < a.M;
-            const double* src = Sb + (ok ? gi : 0) * a.s_pitch + (k0 + kc < Kc ? k0 + kc : 0);
-            cp_async16(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(Kc - k0 - kc) : 0);
-        }
-        if (!XJ) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < (BM * 8 + DM_THREADS - 1) / DM_THREADS; ++q) {
                 const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
-                const int64_t gj = j0 + row;
-                const bool ok = gj < a.N;
-                const double* src = Xb + (ok ? gj : 0) * a.sx_j + (k0 + kc < Kc ? k0 + kc : 0);
-                cp_async16(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(Kc - k0 - kc) : 0);
+                if (BM * 8 % DM_THREADS != 0 && row >= BM) break;
+                const int64_t gi = i0 + row;
+                const bool ok = gi < a.M;
+                const double* src = Sb + (ok ? gi : 0) * a.s_pitch + (k0 + kc < Kc ? k0 + kc : 0);
+                cp_async16(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(Kc - k0 - kc) : 0);
             }
         } else {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = tid + q * DM_THREADS, l = c >> 6, jc = (c & 63) * 2;
-                const int64_t gl = k0 + l;
-                const bool ok = gl < Kc;
-                const double* src = Xb + (ok ? gl : 0) * a.sx_l + (j0 + jc < a.N ? j0 + jc : 0);
-                cp_async16(sX + (uint32_t)(l * DM_PITCH_J + jc) * 8u, src, ok ? clamp_bytes(a.N - j0 - jc) : 0);
+            for (int q = 0; q < BM * 16 / DM_THREADS; ++q) {
+                const int c = tid + q * DM_THREADS, row = c >> 4, kc = c & 15;
+                const bool ok = i0 + row < a.M && k0 + kc < Kc;
+                cp_async8(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, ok ? Sb + (i0 + row) * a.s_pitch + k0 + kc : Sb, ok ? 8 : 0);
+            }
+        }
+        if (!XJ) {
+            if (a.x16) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
+                    const int64_t gj = j0 + row;
+                    const bool ok = gj < a.N;
+                    const double* src = Xb + (ok ? gj : 0) * a.sx_j + (k0 + kc < Kc ? k0 + kc : 0);
+                    cp_async16(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, src, ok ? clamp_bytes(Kc - k0 - kc) : 0);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int c = tid + q * DM_THREADS, row = c >> 4, kc = c & 15;
+                    const bool ok = j0 + row < a.N && k0 + kc < Kc;
+                    cp_async8(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, ok ? Xb + (j0 + row) * a.sx_j + k0 + kc : Xb, ok ? 8 : 0);
+                }
+            }
+        } else {
+            if (a.x16) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = tid + q * DM_THREADS, l = c >> 6, jc = (c & 63) * 2;
+                    const int64_t gl = k0 + l;
+                    const bool ok = gl < Kc;
+                    const double* src = Xb + (ok ? gl : 0) * a.sx_l + (j0 + jc < a.N ? j0 + jc : 0);
+                    cp_async16(sX + (uint32_t)(l * DM_PITCH_J + jc) * 8u, src, ok ? clamp_bytes(a.N - j0 - jc) : 0);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int c = tid + q * DM_THREADS, l = c >> 7, jc = c & 127;
+                    const bool ok = k0 + l < Kc && j0 + jc < a.N;
+                    cp_async8(sX + (uint32_t)(l * DM_PITCH_J + jc) * 8u, ok ? Xb + (k0 + l) * a.sx_l + j0 + jc : Xb, ok ? 8 : 0);
+                }
             }
         }
     };
@@ -256,6 +291,8 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
     if (ksplit < 1) ksplit = 1;
     if (const char* ev = getenv("RBX_DMMA_KSPLIT")) { const int64_t v = atoll(ev); if (v >= 1 && v <= nk) ksplit = v; }
     a.ntiles = tiles; a.ksplit = (int) ksplit; a.partial = nullptr;
+    a.s16 = reinterpret_cast<uintptr_t>(a.S) % 16 == 0 && a.s_pitch % 2 == 0;
+    a.x16 = reinterpret_cast<uintptr_t>(a.X) % 16 == 0 && (a.sx_l == 1 ? a.sx_j : a.sx_l) % 2 == 0;
     a.kper = ((nk + ksplit - 1) / ksplit) * DM_BK;
     a.ksplit = (int)((a.K + a.kper - 1) / a.kper);            // no empty splits
     if (a.ksplit > 1 && ws_alloc(&a.partial, sizeof(double) * (size_t) a.ksplit * (size_t) a.M * (size_t) a.N, stream) != cudaSuccess) {
@@ -277,10 +314,9 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
 
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 1 || g.N < RBX_DMMA_MIN_N || g.K < 64 || (double) g.M * g.N * g.K < 1.3e8) return RBX_ERR_UNSUPPORTED;
-    if (reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
-    if (!((g.sx_l == 1 && g.sx_j % 2 == 0) || (g.sx_j == 1 && g.sx_l % 2 == 0))) return RBX_ERR_UNSUPPORTED;
-    if (g.Sx && (g.ss_l != 1 || g.ss_i % 2 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0)) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 1 || g.N < RBX_DMMA_MIN_N || g.K < 64 || (double) g.M * g.N * g.K < dense_min_macs(1.3e8)) return RBX_ERR_UNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(g.X) % 8 != 0 || (g.sx_l != 1 && g.sx_j != 1)) return RBX_ERR_UNSUPPORTED;
+    if (g.Sx && ((g.ss_l != 1 && g.ss_i != 1) || reinterpret_cast<uintptr_t>(g.Sx) % 8 != 0)) return RBX_ERR_UNSUPPORTED;
     if (g.sc_i != 1 && g.sc_j != 1) return RBX_ERR_UNSUPPORTED;
     if (g.alpha == 0.0) return launch_scale_view<double>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
 
@@ -288,9 +324,27 @@ int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t strea
     a.X = g.X; a.sx_l = g.sx_l; a.sx_j = g.sx_j;
     a.C = g.C; a.sc_i = g.sc_i; a.sc_j = g.sc_j;
     a.M = g.M; a.N = g.N; a.alpha = g.alpha; a.tiles_n = 0;
-    if (g.Sx) {                                   // DenseSkOp::buff given: one pass over the caller's array
+    if (g.Sx && g.ss_l == 1) {                    // DenseSkOp::buff given, k contiguous: one pass over the caller's array
         a.S = g.Sx; a.s_pitch = g.ss_i; a.K = g.K; a.beta = g.beta;
         return launch_dmma_gemm(a, pick_mf(g.M, g.N), stream);
+    }
+    if (g.Sx) {                                   // ... with unit stride along i (a short-axis-major operator): transposed panel by
+        int64_t kp = (((int64_t) 256 << 20) / (8 * g.M)) / 16 * 16;      // panel into a k-contiguous workspace (<= 256 MB) first
+        if (kp < 64) kp = 64;
+        if (kp > g.K) kp = (g.K + 15) / 16 * 16;
+        double* ws = nullptr;
+        if (ws_alloc(&ws, sizeof(double) * (size_t) g.M * (size_t) kp, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+        const int mf = pick_mf(g.M, g.N);
+        int rc = RBX_OK;
+        for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kp) {
+            const int64_t kl = (l0 + kp <= g.K) ? kp : g.K - l0;
+            rc = launch_kmajor_copy<double>(g.Sx + l0 * g.ss_l, kl, g.M, g.ss_l, g.ss_i, ws, kp, stream);
+            if (rc != RBX_OK) break;
+            a.S = ws; a.s_pitch = kp; a.K = kl; a.X = g.X + l0 * g.sx_l; a.beta = (l0 == 0) ? g.beta : 1.0;
+            rc = launch_dmma_gemm(a, mf, stream);
+        }
+        cudaFreeAsync(ws, stream);
+        return rc;
     }
     // implicit operator: k-panels of a fixed-size workspace (<= 256 MB; the CTAs of one row of tiles run together and share
     // their operator rows through L2). Longer panels amortise the read-modify-write of C between panels.

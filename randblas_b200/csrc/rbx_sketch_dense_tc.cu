@@ -26,6 +26,7 @@
 // Everything else returns RBX_ERR_UNSUPPORTED and takes the SIMT kernel.
 #include <cstdlib>
 #include "rbx_kernels.cuh"
+#include "rbx_copy.cuh"
 #include "rbx_tma.cuh"
 
 namespace rbx {
@@ -405,32 +406,6 @@ static int tc_launch(const GemmOperands<float>& g, char mode, const float* Sx, i
     return rc;
 }
 
-// dst[j * pitch + l] = X[l * sx_l + j] for a kl x N piece of data whose rows l are the contiguous ones (unit stride along j):
-// 64 x 64 tiles through shared memory, both sides coalesced
-__global__ void __launch_bounds__(256) tc_kmajor_copy_kernel(const float* __restrict__ src, int64_t kl, int64_t N, int64_t sx_l,
-                                                             float* __restrict__ dst, int64_t pitch) {
-    __shared__ float tile[64][65];
-    const int64_t l0 = (int64_t) blockIdx.x * 64, j0 = (int64_t) blockIdx.y * 64;
-    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
-    for (int ll = ty; ll < 64; ll += 4) {
-        const int64_t l = l0 + ll, j = j0 + tx;
-        tile[ll][tx] = (l < kl && j < N) ? __ldcs(src + l * sx_l + j) : 0.f;
-    }
-    __syncthreads();
-    for (int jj = ty; jj < 64; jj += 4) {
-        const int64_t l = l0 + tx, j = j0 + jj;
-        if (l < kl && j < N) dst[j * pitch + l] = tile[tx][jj];
-    }
-}
-
-// dst[j * pitch + l] = X[l + j * sx_j]: k-contiguous data whose base or leading dimension is not 16-byte aligned, repacked
-__global__ void __launch_bounds__(256) tc_repack_kernel(const float* __restrict__ src, int64_t kl, int64_t N, int64_t sx_j,
-                                                        float* __restrict__ dst, int64_t pitch) {
-    const int64_t j = blockIdx.y;
-    for (int64_t l = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; l < kl; l += (int64_t) gridDim.x * blockDim.x)
-        dst[j * pitch + l] = __ldcs(src + l + j * sx_j);
-}
-
 // Data with unit stride along j instead of along the contraction axis (e.g. RowMajor A in a left sketch, ColMajor A in a
 // right sketch): the tcgen05 kernel wants K-major tiles, so the data is copied chunk by chunk along k into a k-contiguous
 // workspace (at most 512 MB, whatever K is) and every chunk takes the normal path with the operator window advanced and
@@ -448,15 +423,7 @@ static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream)
     int rc = RBX_OK;
     for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kc) {
         const int64_t kl = (l0 + kc <= g.K) ? kc : g.K - l0;
-        if (g.sx_l == 1) {                    // k-contiguous but misaligned: plain repack
-            int64_t bx = (kl + 255) / 256; if (bx > 64) bx = 64;
-            tc_repack_kernel<<<dim3((unsigned) bx, (unsigned) g.N), 256, 0, stream>>>(g.X + l0, kl, g.N, g.sx_j, ws, kc);
-        } else {
-            dim3 grid((unsigned)((kl + 63) / 64), (unsigned)((g.N + 63) / 64));
-            tc_kmajor_copy_kernel<<<grid, 256, 0, stream>>>(g.X + l0 * g.sx_l, kl, g.N, g.sx_l, ws, kc);
-        }
-        count_launch();
-        rc = check_launch("tc_kmajor_copy_kernel");
+        rc = launch_kmajor_copy<float>(g.X + l0 * g.sx_l, kl, g.N, g.sx_l, g.sx_j, ws, kc, stream);   // transposing copy, or a plain repack of misaligned k-contiguous data
         if (rc != RBX_OK) break;
         GemmOperands<float> gp = g;
         gp.X = ws; gp.sx_l = 1; gp.sx_j = kc; gp.K = kl;
@@ -471,19 +438,42 @@ static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream)
     return rc;
 }
 
+// DenseSkOp::buff in a form the kernel cannot read directly (unit stride along i: a short-axis-major operator; a row length
+// or base that is not 16-byte aligned: an odd operator dimension): copied panel by panel into an aligned k-contiguous
+// workspace (<= 512 MB) that the 'X' form of the kernel reads like a generated panel.
+static int tc_via_operator_copy(const GemmOperands<float>& g, cudaStream_t stream) {
+    if (g.ss_l != 1 && g.ss_i != 1) return RBX_ERR_UNSUPPORTED;
+    int64_t kp = (((int64_t) 512 << 20) / (4 * g.M)) / 32 * 32;
+    if (kp < 256) kp = 256;
+    if (kp > g.K) kp = (g.K + 31) / 32 * 32;
+    float* ws = nullptr;
+    if (ws_alloc(&ws, sizeof(float) * (size_t) g.M * (size_t) kp, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+    int rc = RBX_OK;
+    GemmOperands<float> gp = g;
+    for (int64_t l0 = 0; l0 < g.K && rc == RBX_OK; l0 += kp) {
+        const int64_t kl = (l0 + kp <= g.K) ? kp : g.K - l0;
+        rc = launch_kmajor_copy<float>(g.Sx + l0 * g.ss_l, kl, g.M, g.ss_l, g.ss_i, ws, kp, stream);
+        if (rc != RBX_OK) break;
+        gp.K = kl; gp.X = g.X + l0; gp.beta = (l0 == 0) ? g.beta : 1.f;
+        rc = tc_launch(gp, 'X', ws, kp, stream);
+    }
+    cudaFreeAsync(ws, stream);
+    return rc;
+}
+
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
     const bool j_major = g.sx_l != 1 && g.sx_j == 1;
     const bool k_major_misaligned = g.sx_l == 1 && g.N >= 2 && g.N <= 65535 && ((g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0);
-    if ((j_major || k_major_misaligned) && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= 512 && (double) g.M * g.N * g.K >= 1e8 &&
+    if ((j_major || k_major_misaligned) && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= 512 && (double) g.M * g.N * g.K >= dense_min_macs(1e8) &&
         !getenv("RBX_TC_NO_COPY"))
         return tc_via_kmajor_copy(g, stream);
     if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 1 || g.N < RBX_TC_MIN_N || g.K < 256 || (double) g.M * g.N * g.K < 1e8) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 1 || g.N < RBX_TC_MIN_N || g.K < 256 || (double) g.M * g.N * g.K < dense_min_macs(1e8)) return RBX_ERR_UNSUPPORTED;
     if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;
     if (g.alpha == 0.f) return launch_scale_view<float>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
     if (g.Sx) {      // DenseSkOp::buff given: k-contiguous rows, 16-byte aligned, no ragged float4 at the end of a row
-        if (g.ss_l != 1 || g.ss_i % 4 != 0 || g.K % 4 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0) return RBX_ERR_UNSUPPORTED;
+        if (g.ss_l != 1 || g.ss_i % 4 != 0 || g.K % 4 != 0 || reinterpret_cast<uintptr_t>(g.Sx) % 16 != 0) return tc_via_operator_copy(g, stream);
         return tc_launch(g, 'X', g.Sx, g.ss_i, stream);
     }
     // Implicit operator. The fused kernel generates the operator tile from the counter inside the CTA; it needs the parent

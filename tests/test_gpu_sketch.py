@@ -233,6 +233,30 @@ def test_sketch_general_dense_dmma_path(rb, cuda, monkeypatch):
             assert rb.lib.rbx_launch_count() - l0 >= 2, (dt, layout, d, n, m)
 
 
+def test_dense_tensor_core_paths_take_misaligned_operands(rb, cuda):
+    """operands the 16-byte copies of the tensor-core kernels cannot read as they are still run on those kernels, not on the
+    SIMT fallback (1 launch): double data with an odd leading dimension in either layout (8-byte staging copies in the DMMA
+    kernel); a pre-filled operator with an odd row length or a window offset that breaks the alignment (DMMA: 8-byte copies;
+    tcgen05: repacked panel); a pre-filled short-axis-major operator, whose unit stride runs along the sketch dimension
+    (transposed panel by panel into a k-contiguous workspace in both precisions)."""
+    def launches(**kw):
+        l0 = rb.lib.rbx_launch_count()
+        assert run_dense_case(rb, cuda, **kw) < 0.05
+        return rb.lib.rbx_launch_count() - l0
+    base = dict(side="L", opS="N", opA="N", alpha=1.5, beta=-0.5)
+    # implicit operator, double, odd lda: operator panel fill + DMMA GEMM (+ split-K reduce)
+    assert launches(dt="f64", layout="C", d=200, n=260, m=4101, **base) >= 2
+    assert launches(dt="f64", layout="R", d=130, n=261, m=4100, off=(3, 1), D_extra=(2, 2), **base) >= 2
+    assert launches(dt="f64", layout="C", d=200, n=260, m=4100, lda_pad=3, **base) >= 2
+    # pre-filled operators: fill_dense(S) is one launch and the SIMT kernel one more
+    for dt in ("f32", "f64"):
+        assert launches(dt=dt, layout="C", d=192, n=256, m=4099, prefilled=True, **base) >= 3                       # odd row length
+        assert launches(dt=dt, layout="C", d=192, n=256, m=4096, prefilled=True, off=(1, 3), D_extra=(2, 2), **base) >= 3  # window offset
+        assert launches(dt=dt, layout="C", d=192, n=256, m=4096, prefilled=True, ma="S", **base) >= 3               # unit stride along i
+        assert launches(dt=dt, layout="R", d=190, n=300, m=4101, prefilled=True, ma="S", off=(2, 5), D_extra=(1, 1), **base) >= 3
+        assert launches(dt=dt, side="R", layout="R", opS="N", opA="N", alpha=1.0, beta=2.0, d=256, n=4100, m=300, prefilled=True, ma="S") >= 3
+
+
 def test_nan_in_B_is_overwritten_when_beta_is_zero(rb, cuda):
     """util::safe_scal (util.hh:51-59) / BLAS convention: beta == 0 never reads B"""
     S = rb.DenseSkOp(rb.DenseDist(4, 9), 1)
