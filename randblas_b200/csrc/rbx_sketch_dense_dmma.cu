@@ -20,6 +20,9 @@
 #ifndef RBX_DMMA_MIN_N
 #define RBX_DMMA_MIN_N 2         // tall-skinny data: with split-K the padded 128-column tile beats the SIMT kernel
 #endif
+#ifndef RBX_DMMA_MIN_K
+#define RBX_DMMA_MIN_K 16        // a short contraction axis (lifts): one k-tile is enough to beat the SIMT kernel
+#endif
 namespace rbx {
 
 constexpr int DM_BM = 128, DM_BN = 128, DM_BK = 16, DM_STAGES = 4, DM_THREADS = 256;
@@ -314,7 +317,7 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
 
 int launch_sketch_dense_tc_f64(const GemmOperands<double>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 1 || g.N < RBX_DMMA_MIN_N || g.K < 64 || (double) g.M * g.N * g.K < dense_min_macs(1.3e8)) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 1 || g.N < RBX_DMMA_MIN_N || g.K < RBX_DMMA_MIN_K || (double) g.M * g.N * g.K < dense_min_macs(1.3e8)) return RBX_ERR_UNSUPPORTED;
     if (reinterpret_cast<uintptr_t>(g.X) % 8 != 0 || (g.sx_l != 1 && g.sx_j != 1)) return RBX_ERR_UNSUPPORTED;
     if (g.Sx && ((g.ss_l != 1 && g.ss_i != 1) || reinterpret_cast<uintptr_t>(g.Sx) % 8 != 0)) return RBX_ERR_UNSUPPORTED;
     if (g.sc_i != 1 && g.sc_j != 1) return RBX_ERR_UNSUPPORTED;

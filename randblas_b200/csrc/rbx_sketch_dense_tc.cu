@@ -35,6 +35,9 @@ constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32;
 #ifndef RBX_TC_MIN_N
 #define RBX_TC_MIN_N 2        // tall-skinny data: the padded 256-column tile still beats the SIMT kernel 17-27x (measured at n = 4 .. 48)
 #endif
+#ifndef RBX_TC_MIN_K
+#define RBX_TC_MIN_K 32       // a short contraction axis ("lifts", B = S A with a tall S): the kernel is bound by its epilogue there and still 2-5x ahead of the SIMT kernel
+#endif
 #ifndef TC_X_HI_RAW
 #define TC_X_HI_RAW 1
 #endif
@@ -463,13 +466,16 @@ static int tc_via_operator_copy(const GemmOperands<float>& g, cudaStream_t strea
 
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
+    // shortest contraction axis worth the kernel: its epilogue writes C along i (one row per TMEM lane), which is uncoalesced when
+    // C's unit stride is along j, and a short contraction ("lift") is all epilogue: measured cross-over K ~ 80 there (tools/micro/lift_dense.py)
+    const int64_t min_k = (g.sc_i == 1) ? RBX_TC_MIN_K : 96;
     const bool j_major = g.sx_l != 1 && g.sx_j == 1;
     const bool k_major_misaligned = g.sx_l == 1 && g.N >= 2 && g.N <= 65535 && ((g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0);
-    if ((j_major || k_major_misaligned) && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= 512 && (double) g.M * g.N * g.K >= dense_min_macs(1e8) &&
+    if ((j_major || k_major_misaligned) && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= min_k && (double) g.M * g.N * g.K >= dense_min_macs(1e8) &&
         !getenv("RBX_TC_NO_COPY"))
         return tc_via_kmajor_copy(g, stream);
     if (g.sx_l != 1 || g.N < 2 || (g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0) return RBX_ERR_UNSUPPORTED;
-    if (g.M < 1 || g.N < RBX_TC_MIN_N || g.K < 256 || (double) g.M * g.N * g.K < dense_min_macs(1e8)) return RBX_ERR_UNSUPPORTED;
+    if (g.M < 1 || g.N < RBX_TC_MIN_N || g.K < min_k || (double) g.M * g.N * g.K < dense_min_macs(1e8)) return RBX_ERR_UNSUPPORTED;
     if (g.K > 0x7fffffffll - TC_BK || g.N > 0x7fffffffll - TC_BN) return RBX_ERR_UNSUPPORTED;
     if (g.alpha == 0.f) return launch_scale_view<float>(g.C, g.M, g.N, g.sc_i, g.sc_j, g.beta, stream);
     if (g.Sx) {      // DenseSkOp::buff given: k-contiguous rows, 16-byte aligned, no ragged float4 at the end of a row

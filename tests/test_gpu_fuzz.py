@@ -45,7 +45,7 @@ def test_fuzz_sketch_general_dense(rb, cuda, monkeypatch, block, macs):
     for it in range(14):
         dt, side, layout = pick(rng, ["f32", "f64"]), pick(rng, "LR"), pick(rng, "CR")
         opS, opA = pick(rng, "NNT"), pick(rng, "NNT")
-        d, n, m = logint(rng, 1, 300), logint(rng, 1, 300), logint(rng, 1 if rng.random() < 0.3 else 256, 6000)
+        d, n, m = logint(rng, 1, 300), logint(rng, 1, 300), logint(rng, 1 if rng.random() < 0.3 else 16, 6000)
         if rng.random() < 0.2:
             d, m = m % 700 + 1, d            # lifts: the operator's long axis is not the contraction
         if side == "R":
