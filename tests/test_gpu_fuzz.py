@@ -54,7 +54,9 @@ def test_fuzz_sketch_general_dense(rb, cuda, monkeypatch, block, macs):
         draw = dict(dt=dt, side=side, layout=layout, opS=opS, opA=opA, d=d, n=n, m=m, alpha=alpha, beta=beta, off=small_offsets(rng),
                     D_extra=small_offsets(rng), fam=pick(rng, "GU"), ma=pick(rng, "LS"), lda_pad=pick(rng, [0, 0, 1, 2, 3, 4, 8]),
                     ldb_pad=pick(rng, [0, 0, 1, 3, 4]), key=(int(rng.integers(0, 2 ** 32)), int(rng.integers(0, 2 ** 32))),
-                    prefilled=bool(rng.random() < 0.2))
+                    prefilled=bool(rng.random() < 0.2), host=bool(rng.random() < 0.2))
+        if draw["host"]:
+            draw["prefilled"] = False        # host-pointer sketches take implicit operators
         l0 = rb.lib.rbx_launch_count()
         try:
             run_dense_case(rb, cuda, **draw)
@@ -90,7 +92,7 @@ def test_fuzz_sketch_general_sparse_operator(rb, cuda, block):
         k = min(short, pick(rng, [1, 2, 3, 4, 7, 8, 8, 8, 13, 32, 33, 40]))
         draw = dict(dt=dt, side=side, layout=layout, opS=opS, opA=opA, d=d, n=n, m=m, alpha=alpha, beta=beta, k=k, ma=pick(rng, "SSL"),
                     D_extra=extra, off=off, key=int(rng.integers(0, 2 ** 31)), lda_pad=pick(rng, [0, 0, 1, 2, 4]),
-                    filled=bool(rng.random() < 0.25))
+                    filled=bool(rng.random() < 0.25), host=bool(rng.random() < 0.2))
         try:
             run_sparseop_case(rb, cuda, **draw)
         except Exception as e:
@@ -107,7 +109,7 @@ def test_fuzz_sketch_sparse(rb, cuda, block):
         alpha, beta = pick(rng, SCALARS)
         draw = dict(dt=dt, side=side, layout=layout, opS=pick(rng, "NNT"), opA=pick(rng, "NNT"), d=d, n=n, m=m, alpha=alpha, beta=beta,
                     fmt=fmt, density=pick(rng, [0.0, 0.004, 0.02, 0.1, 0.5]), off_s=small_offsets(rng),
-                    off_a=small_offsets(rng) if fmt == "O" else (0, 0), fam=pick(rng, "GU"), ma=pick(rng, "LS"))
+                    off_a=small_offsets(rng) if fmt == "O" else (0, 0), fam=pick(rng, "GU"), ma=pick(rng, "LS"), host=bool(rng.random() < 0.25))
         try:
             run_sparsedata_case(rb, cuda, **draw)
         except Exception as e:
@@ -210,3 +212,32 @@ def test_fuzz_fill_sparse_bits(rb, cuda, block):
         assert np.array_equal(S.rows.cpu().numpy(), rows) and np.array_equal(S.cols.cpu().numpy(), cols), f"fill_sparse indices, draw {block}.{it}: {what}"
         assert np.array_equal(bits(S.vals.cpu().numpy()), bits(vals)), f"fill_sparse values, draw {block}.{it}: {what}"
         assert list(S.next_state.counter) == list(exp_next), f"fill_sparse next state, draw {block}.{it}: {what}"
+
+
+# ---------------------------------------------------------------------------------------------- medium sizes, shipping dispatch
+@pytest.mark.parametrize("block", range(2 * MORE))
+def test_fuzz_medium_sizes(rb, cuda, block):
+    """draws large enough (1e8 .. 1e10 multiply-adds) for the shipping dispatch to pick the tensor-core and streaming kernels"""
+    rng = np.random.default_rng(7000 + block)
+    for it in range(6):
+        dt, side, layout = pick(rng, ["f32", "f64"]), pick(rng, "LR"), pick(rng, "CR")
+        alpha, beta = pick(rng, SCALARS)
+        d, n, m = logint(rng, 8, 700), logint(rng, 2, 900), logint(rng, 2000, 60000)
+        while d * m > 2e7:
+            d, m = max(1, d * 2 // 3), max(1, m * 2 // 3)
+        if side == "R":
+            n, m = m, n
+        draw = dict(dt=dt, side=side, layout=layout, opS=pick(rng, "NNT"), opA=pick(rng, "NNT"), d=d, n=n, m=m, alpha=alpha, beta=beta,
+                    off=small_offsets(rng), D_extra=small_offsets(rng), fam=pick(rng, "GU"), ma=pick(rng, "LS"), lda_pad=pick(rng, [0, 0, 1, 3, 4]),
+                    ldb_pad=pick(rng, [0, 0, 1, 4]), key=(int(rng.integers(0, 2 ** 32)), 0), prefilled=bool(rng.random() < 0.25))
+        try:
+            run_dense_case(rb, cuda, **draw)
+        except Exception as e:
+            raise AssertionError(f"medium dense draw {block}.{it}: {draw}: {e}") from e
+        k = pick(rng, [1, 4, 8, 8, 8, 16, 32, 40])
+        sdraw = dict(dt=dt, side=side, layout=layout, opS=draw["opS"], opA=draw["opA"], d=d, n=n, m=m, alpha=alpha, beta=beta, k=min(k, d),
+                     ma=pick(rng, "SSSL"), D_extra=draw["D_extra"], off=draw["off"], key=int(rng.integers(0, 2 ** 31)), lda_pad=draw["lda_pad"])
+        try:
+            run_sparseop_case(rb, cuda, **sdraw)
+        except Exception as e:
+            raise AssertionError(f"medium sparse-operator draw {block}.{it}: {sdraw}: {e}") from e

@@ -44,7 +44,8 @@ def check_bound(dt, got, B0, Sop, Aop, alpha, beta, side, what):
 
 
 def run_dense_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, D_extra=(0, 0), off=(0, 0), fam="G", ma="L",
-                   lda_pad=0, ldb_pad=0, key=(3, 0), prefilled=False):
+                   lda_pad=0, ldb_pad=0, key=(3, 0), prefilled=False, host=False):
+    """host=True: A and B stay in host memory (the rbx_host_* entry points stage them)"""
     rng = np.random.default_rng(d * 131 + n * 17 + m)
     npdt = np.float32 if dt == "f32" else np.float64
     if side == "L":
@@ -66,7 +67,8 @@ def run_dense_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, D
     S = rb.DenseSkOp(rb.DenseDist(Dr, Dc, fam, ma), rb.RNGState(list(key)), dtype=TDT[dt])
     if prefilled:
         rb.fill_dense(S)
-    dA, dB = torch.from_numpy(A).to(cuda), torch.from_numpy(B0.copy()).to(cuda)
+    where = "cpu" if host else cuda
+    dA, dB = torch.from_numpy(A).to(where), torch.from_numpy(B0.copy()).to(where)
     L, O = rb.Layout(layout), rb.Op
     if side == "L":
         rb.sketch_general(L, O(opS), O(opA), *dims, alpha, S, off[0], off[1], dA, lda, beta, dB, ldb)
@@ -280,7 +282,7 @@ def sparse_S_dense(dt, r, c, k, ma, ctr, key):
 
 
 def run_sparseop_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, k, ma, D_extra=(0, 0), off=(0, 0), key=42,
-                      lda_pad=0, filled=False):
+                      lda_pad=0, filled=False, host=False):
     rng = np.random.default_rng(d * 7 + n * 3 + m + k)
     npdt = np.float32 if dt == "f32" else np.float64
     if side == "L":
@@ -299,7 +301,8 @@ def run_sparseop_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta
     S = rb.SparseSkOp(rb.SparseDist(Sr, Sc, k, ma), key, dtype=TDT[dt])
     if filled:
         rb.fill_sparse(S)
-    dA, dB = torch.from_numpy(A).to(cuda), torch.from_numpy(B0.copy()).to(cuda)
+    where = "cpu" if host else cuda
+    dA, dB = torch.from_numpy(A).to(where), torch.from_numpy(B0.copy()).to(where)
     L, O = rb.Layout(layout), rb.Op
     if side == "L":
         rb.sketch_general(L, O(opS), O(opA), *dims, alpha, S, off[0], off[1], dA, lda, beta, dB, ldb)
@@ -550,7 +553,8 @@ def to_fmt(rb, cuda, M, fmt):
     return rb.CSCMatrix(M.shape[0], M.shape[1], t(c.data), t(c.indices, np.int64), t(c.indptr, np.int64))
 
 
-def run_sparsedata_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, fmt, density, off_s=(0, 0), off_a=(0, 0), fam="G", ma="L"):
+def run_sparsedata_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, beta, fmt, density, off_s=(0, 0), off_a=(0, 0), fam="G", ma="L",
+                        host=False):
     rng = np.random.default_rng(d + 3 * n + 7 * m + int(100 * density))
     npdt = np.float32 if dt == "f32" else np.float64
     if side == "L":
@@ -564,10 +568,11 @@ def run_sparsedata_case(rb, cuda, dt, side, layout, opS, opA, d, n, m, alpha, be
     Dr, Dc = rowsS + off_s[0] + 2, colsS + off_s[1] + 1
     Ar, Ac = rowsA + off_a[0] + (3 if fmt == "O" and off_a != (0, 0) else 0), colsA + off_a[1]
     Afull = random_sparse(rng, Ar, Ac, density, npdt)
-    Asp = to_fmt(rb, cuda, Afull, fmt)
+    where = "cpu" if host else cuda
+    Asp = to_fmt(rb, where, Afull, fmt)
     ldb = rowsB if layout == "C" else colsB
     B0 = rng.standard_normal(rowsB * colsB).astype(npdt)
-    dB = torch.from_numpy(B0.copy()).to(cuda)
+    dB = torch.from_numpy(B0.copy()).to(where)
     S = rb.DenseSkOp(rb.DenseDist(Dr, Dc, fam, ma), 11, dtype=TDT[dt])
     L, O = rb.Layout(layout), rb.Op
     if side == "L":
