@@ -216,8 +216,33 @@ def test_fill_sparse_random_vs_oracle(rb, cuda):
             assert S.next_state.counter == nxt
 
 
+def test_fill_sparse_long_vectors_hash_kernel(rb, cuda, monkeypatch):
+    """16 < vec_nnz <= 8192: one CTA per vector with the lazily kept work array in shared memory (direct array below vec_nnz, hash
+    table above), 128 shuffle steps at a time resolved in rounds of steps that do not interact. Cases where almost no steps
+    interact (vec_nnz << the sampled axis), where almost all do (a full permutation of the axis), several groups of steps, the
+    largest table, and one step beyond it (the global work-array kernel); always the oracle's indices and signs, and the same
+    as with the kernel off."""
+    cases = [(300, 5000, 300, "S"), (3000, 3000, 3000, "S"), (64, 50000, 4096, "L"), (200, 9000, 8192, "L"), (9000, 150, 8193, "L"),
+             (2048, 40000, 33, "S"), (5000, 700, 513, "S"), (100, 1 << 20, 1000, "L"), (64, 70000, 17, "S"), (20, 3000, 20, "S"), (129, 129, 129, "S")]
+    for (r, c, k, ma) in cases:
+        key, ctr = [k * 7 + r, 1], [0xFFFFFFF0, 0xFFFFFFFF, 3, 0]
+        S = rb.SparseSkOp(rb.SparseDist(r, c, k, ma), rb.RNGState(key, ctr), dtype=torch.float32, index_dtype=torch.int32)
+        rb.fill_sparse(S)
+        rc, rows, cols, vals, nxt = ol.fill_sparse("f32", "i32", r, c, k, ma, ctr, key)
+        assert rc == 0
+        assert np.array_equal(S.rows.cpu().numpy(), rows) and np.array_equal(S.cols.cpu().numpy(), cols), (r, c, k, ma)
+        assert np.array_equal(S.vals.cpu().numpy(), vals) and S.next_state.counter == nxt
+    monkeypatch.setenv("RBX_FY_NO_HASH", "1")
+    for (r, c, k, ma) in cases[:3]:
+        S = rb.SparseSkOp(rb.SparseDist(r, c, k, ma), 5); rb.fill_sparse(S)
+        monkeypatch.delenv("RBX_FY_NO_HASH")
+        S2 = rb.SparseSkOp(rb.SparseDist(r, c, k, ma), 5); rb.fill_sparse(S2)
+        monkeypatch.setenv("RBX_FY_NO_HASH", "1")
+        assert torch.equal(S.rows, S2.rows) and torch.equal(S.cols, S2.cols) and torch.equal(S.vals, S2.vals)
+
+
 def test_repeated_fisher_yates_workarray_path(rb, cuda):
-    """vec_nnz > 128 takes the explicit work-array kernel; same stream as the lazy kernel and the oracle"""
+    """repeated_fisher_yates as its own entry point (vec_nnz = 200: the per-CTA hash kernel); same stream as the oracle"""
     k, n, r = 200, 1000, 37
     idx = torch.empty(k * r, dtype=torch.int64, device=cuda)
     rb.repeated_fisher_yates(rb.RNGState(7), k, n, r, idx)
