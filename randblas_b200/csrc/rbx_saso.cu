@@ -259,6 +259,7 @@ struct SasoArgs {
     int stream_stride, rec_stride, ws_stride;
     int CK, cap;                                       // rows per chunk; tail elements a row block's region holds
     int nbuckets, njb, nrb, msplit, nchunks, dbg_skip;
+    int x_elem;                                        // row-contiguous data whose rows are not 16-byte aligned: element-wise copies
     int direct;                                        // 1: one split and no row copies -> the tile kernel stores alpha * acc + beta * C itself
     int64_t M;                                         // rows the tile kernel owns (R copies of the window's rows when R > 1)
     T alpha, beta;
@@ -466,7 +467,23 @@ __global__ void __launch_bounds__(SASO_TILE_THREADS, 1) saso_tile_kernel(const S
         const uint32_t st = smem0 + (uint32_t) s * stage_bytes;
         const bool inside = cols_inside && (int64_t)(ch + 1) * CK <= a.K;
         if (!COLS_CONTIG) {
-            if (inside) {
+            if (a.x_elem) {
+                // rows that do not start on 16 bytes (an odd leading dimension or base): one element per copy, a warp instruction
+                // still moves whole 128-byte row segments
+                if (inside) {
+                    const T* src = a.X + ((int64_t) ch * CK + lt / W) * a.sx_l + j0 + lt % W;
+                    const int64_t step = (int64_t)(LT / W) * a.sx_l;
+                    uint32_t dst = st + (lt / W) * SASO_ROWB + (lt % W) * (int) sizeof(T);
+#pragma unroll 8
+                    for (int i = 0; i < CK / (LT / W); ++i) { cp_async_small<(int) sizeof(T)>(dst, src, (uint32_t) sizeof(T)); dst += (LT / W) * SASO_ROWB; src += step; }
+                } else
+                for (int p = lt; p < CK * W; p += LT) {
+                    const int row = p / W, q = p % W;
+                    const int64_t l = (int64_t) ch * CK + row, col = j0 + q;
+                    const uint32_t nb = (l < a.K && col < a.N) ? (uint32_t) sizeof(T) : 0u;
+                    cp_async_small<(int) sizeof(T)>(st + row * SASO_ROWB + q * (int) sizeof(T), nb ? a.X + l * a.sx_l + col : a.X, nb);
+                }
+            } else if (inside) {
                 const T* src = a.X + ((int64_t) ch * CK + (lt >> 3)) * a.sx_l + j0 + (lt & 7) * EP;
                 const int64_t step = (int64_t)(LT / 8) * a.sx_l;
                 uint32_t dst = st + lt * 16;
@@ -648,9 +665,10 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     if (!cols_contig && sx_j != 1) return RBX_ERR_UNSUPPORTED;
     if (vec_nnz > 32 || M > SASO_MAX_RB * SASO_R || M < 1 || N < 1 || K < 64) return RBX_ERR_UNSUPPORTED;
     const int64_t ld = cols_contig ? sx_j : sx_l;
-    // row-contiguous data is staged with 16-byte cp.async (base and leading dimension 16-byte aligned); column-contiguous
-    // data goes element by element (8 / 4-byte cp.async) and needs nothing beyond the natural alignment of T
-    if (!cols_contig && (reinterpret_cast<uintptr_t>(X) % 16 != 0 || (ld * (int64_t) sizeof(T)) % 16 != 0)) return RBX_ERR_UNSUPPORTED;
+    // row-contiguous data is staged with 16-byte cp.async when its base and leading dimension are 16-byte aligned, element by
+    // element otherwise; column-contiguous data always goes element by element (8 / 4-byte cp.async): nothing beyond the
+    // natural alignment of T is required
+    const bool x_elem = !cols_contig && (reinterpret_cast<uintptr_t>(X) % 16 != 0 || (ld * (int64_t) sizeof(T)) % 16 != 0);
     if (reinterpret_cast<uintptr_t>(X) % sizeof(T) != 0) return RBX_ERR_UNSUPPORTED;
     if (K > (int64_t) 0x7fffffff - 512 || N > 0x7fffffff) return RBX_ERR_UNSUPPORTED;
     if (alpha == (T) 0) return launch_scale_view<T>(C, M, N, sc_i, sc_j, beta, stream);
@@ -729,7 +747,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         a.CK = CK; a.cap = cap;
         a.nbuckets = nbuckets; a.njb = njb; a.nrb = nrb; a.msplit = msplit; a.nchunks = nchunks;
         a.dbg_skip = getenv("RBX_SASO_SKIP") ? atoi(getenv("RBX_SASO_SKIP")) : 0;
-        a.M = Mv; a.direct = direct ? 1 : 0;
+        a.M = Mv; a.direct = direct ? 1 : 0; a.x_elem = x_elem ? 1 : 0;
         a.alpha = alpha; a.beta = beta; a.C = C; a.sc_i = sc_i; a.sc_j = sc_j; a.partial = partial; a.spill_flag = flag;
         const unsigned grid = (unsigned)(njb * msplit * nrb);
         const size_t smem = nst * stage;

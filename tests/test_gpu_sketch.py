@@ -352,13 +352,17 @@ def test_saso_medium(rb, cuda, dt):
         run_sparseop_case(rb, cuda, dt, "R", layout, "N", "N", 256, 96, 16384, 1.0, 0.0, 8, "S", key=1997)
         run_sparseop_case(rb, cuda, dt, "R", layout, "N", "T", 200, 100, 10001, 2.0, 1.0, 8, "S", key=1997, off=(1234, 5), D_extra=(77, 51))
         run_sparseop_case(rb, cuda, dt, "L", layout, "T", "N", 256, 96, 16384, 1.5, 0.0, 8, "S", key=3)
-    # column-contiguous data whose leading dimension is not a multiple of 16 bytes still takes the streaming kernel (its
-    # element-wise cp.async needs only the natural alignment): prep + tile + spill variant + reduce = 4 launches, not the
-    # general path's regroup; row-contiguous data with such a leading dimension takes the general path
+    # data whose leading dimension is not a multiple of 16 bytes still takes the streaming kernel (element-wise cp.async needs
+    # only the natural alignment): prep + tile + spill variant + reduce = 4 launches, not the general path's regroup
     l0 = rb.lib.rbx_launch_count()
     run_sparseop_case(rb, cuda, dt, "L", "C", "N", "N", 256, 96, 16384, 1.0, 0.5, 8, "S", key=11, lda_pad=1)
     assert rb.lib.rbx_launch_count() - l0 <= 4
+    l0 = rb.lib.rbx_launch_count()
     run_sparseop_case(rb, cuda, dt, "L", "R", "N", "N", 256, 97, 16384, 1.0, 0.5, 8, "S", key=11, lda_pad=0)
+    assert rb.lib.rbx_launch_count() - l0 <= 4
+    l0 = rb.lib.rbx_launch_count()
+    run_sparseop_case(rb, cuda, dt, "L", "R", "N", "N", 300, 40, 9000, 1.5, 0.0, 8, "S", key=12, lda_pad=3, off=(2, 77), D_extra=(5, 9))
+    assert rb.lib.rbx_launch_count() - l0 <= 4
 
 
 @pytest.mark.parametrize("dt", ["f32", "f64"])
