@@ -314,10 +314,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sketch_dense_tc_kernel(const __
         constexpr int CG = TC_BN / (TC_EPI_WARPS / 4);     // columns per epilogue warp
         const int cgrp = (warp - 2) >> 2;                  // which group of the BN columns
         const int64_t row = i0 + lg * 32 + lane;
+        const bool vec_rows = a.ksplit == 1 && a.sc_j == 1 && (a.sc_i & 3) == 0 && (reinterpret_cast<uintptr_t>(a.C) & 15) == 0;
         for (int c0 = cgrp * CG; c0 < (cgrp + 1) * CG && warp - 2 < TC_EPI_WARPS; c0 += 32) {
             uint32_t v[32];
             tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t) c0, v);
-            if (row < a.M) {
+            if (row < a.M && vec_rows && j0 + c0 + 32 <= a.N) {
+                // C with unit stride along j: the thread's 32 consecutive columns of its row go out as eight 16-byte stores
+                float4* cp = reinterpret_cast<float4*>(a.C + row * a.sc_i + j0 + c0);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    float4 o;
+                    o.x = a.alpha * ((nit > 0) ? __uint_as_float(v[4 * q + 0]) : 0.f); o.y = a.alpha * ((nit > 0) ? __uint_as_float(v[4 * q + 1]) : 0.f);
+                    o.z = a.alpha * ((nit > 0) ? __uint_as_float(v[4 * q + 2]) : 0.f); o.w = a.alpha * ((nit > 0) ? __uint_as_float(v[4 * q + 3]) : 0.f);
+                    if (a.beta != 0.f) { const float4 old = cp[q]; o.x += a.beta * old.x; o.y += a.beta * old.y; o.z += a.beta * old.z; o.w += a.beta * old.w; }
+                    cp[q] = o;
+                }
+            } else if (row < a.M) {
 #pragma unroll
                 for (int q = 0; q < 32; ++q) {
                     const int64_t col = j0 + c0 + q;
@@ -417,6 +429,30 @@ static int tc_via_kmajor_copy(const GemmOperands<float>& g, cudaStream_t stream)
     if (g.N > 65535ll * 64) return RBX_ERR_UNSUPPORTED;
     int64_t budget = (int64_t) 512 << 20;
     if (const char* ev = getenv("RBX_TC_COPY_MB")) { const int64_t v = atoll(ev); if (v >= 1) budget = v << 20; }     // tests: several chunks at small sizes
+    // Many columns: chunk along j with the whole contraction axis in the workspace, so that every column block of C is written
+    // once. (Chunks along k make every chunk after the first read C back and add to it: at 2048 x 4096 x 65536 that doubled the
+    // time, at 256 x 4096 x 262144 it was 5.5x.) An implicit Gaussian operator is regenerated per block -- 169 / nb of the block's
+    // tensor time -- hence the lower bound on the block width.
+    const int64_t kpad = (g.K + 31) / 32 * 32;
+    const int64_t nb = (budget / (4 * kpad)) / TC_BN * TC_BN;
+    if ((nb >= 1024 || nb >= g.N) && nb >= TC_BN && !getenv("RBX_TC_COPY_ALONG_K")) {
+        const int64_t wcols = nb < g.N ? nb : g.N;
+        float* ws = nullptr;
+        if (ws_alloc(&ws, sizeof(float) * (size_t) wcols * (size_t) kpad, stream) != cudaSuccess) { cudaGetLastError(); return RBX_ERR_ALLOC; }
+        int rc = RBX_OK;
+        for (int64_t j0 = 0; j0 < g.N && rc == RBX_OK; j0 += nb) {
+            const int64_t nl = (j0 + nb <= g.N) ? nb : g.N - j0;
+            rc = launch_kmajor_copy<float>(g.X + j0 * g.sx_j, g.K, nl, g.sx_l, g.sx_j, ws, kpad, stream);
+            if (rc != RBX_OK) break;
+            GemmOperands<float> gp = g;
+            gp.X = ws; gp.sx_l = 1; gp.sx_j = kpad; gp.N = nl; gp.C = g.C + j0 * g.sc_j;
+            if (nl < RBX_TC_MIN_N) { rc = launch_sketch_dense_simt<float>(gp, stream); continue; }     // a last block of one column
+            rc = launch_sketch_dense_tc_f32(gp, stream);
+            if (rc == RBX_ERR_UNSUPPORTED) rc = launch_sketch_dense_simt<float>(gp, stream);          // a narrow last block below the work threshold
+        }
+        cudaFreeAsync(ws, stream);
+        return rc;
+    }
     int64_t kc = (budget / (4 * g.N)) / 32 * 32;
     if (kc < 512) return RBX_ERR_UNSUPPORTED;
     const int64_t nch = (g.K + kc - 1) / kc;
@@ -466,9 +502,11 @@ static int tc_via_operator_copy(const GemmOperands<float>& g, cudaStream_t strea
 
 int launch_sketch_dense_tc_f32(const GemmOperands<float>& g, cudaStream_t stream) {
     if (getenv("RBX_NO_TC")) return RBX_ERR_UNSUPPORTED;
-    // shortest contraction axis worth the kernel: its epilogue writes C along i (one row per TMEM lane), which is uncoalesced when
-    // C's unit stride is along j, and a short contraction ("lift") is all epilogue: measured cross-over K ~ 80 there (tools/micro/lift_dense.py)
-    const int64_t min_k = (g.sc_i == 1) ? RBX_TC_MIN_K : 96;
+    // shortest contraction axis worth the kernel. A short contraction ("lift") is all epilogue; the epilogue holds one row of C per
+    // TMEM lane: coalesced when C's unit stride is along i, 16-byte vector stores when it is along j and the rows are 16-byte
+    // aligned, scalar and uncoalesced otherwise (measured cross-over K ~ 80 there, tools/micro/lift_dense.py)
+    const bool c_rows_vec = g.sc_j == 1 && (g.sc_i & 3) == 0 && (reinterpret_cast<uintptr_t>(g.C) & 15) == 0;
+    const int64_t min_k = (g.sc_i == 1 || c_rows_vec) ? RBX_TC_MIN_K : 96;
     const bool j_major = g.sx_l != 1 && g.sx_j == 1;
     const bool k_major_misaligned = g.sx_l == 1 && g.N >= 2 && g.N <= 65535 && ((g.sx_j * 4) % 16 != 0 || reinterpret_cast<uintptr_t>(g.X) % 16 != 0);
     if ((j_major || k_major_misaligned) && g.N >= RBX_TC_MIN_N && g.M >= 1 && g.K >= min_k && (double) g.M * g.N * g.K >= dense_min_macs(1e8) &&
