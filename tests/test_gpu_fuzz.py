@@ -241,3 +241,89 @@ def test_fuzz_medium_sizes(rb, cuda, block):
             run_sparseop_case(rb, cuda, **sdraw)
         except Exception as e:
             raise AssertionError(f"medium sparse-operator draw {block}.{it}: {sdraw}: {e}") from e
+
+
+# ---------------------------------------------------------------------------------------------- spmm, symmetric
+@pytest.mark.parametrize("block", range(3 * MORE))
+def test_fuzz_left_right_spmm(rb, cuda, block):
+    """sparse_data::left_spmm / right_spmm (spmm_dispatch.hh:48-200) with random formats, layouts, transposes, scalars, leading
+    dimensions and (COO) sub-matrix offsets, against a dense product"""
+    from test_gpu_sketch import mat, random_sparse, span, to_fmt
+    rng = np.random.default_rng(8000 + block)
+    for it in range(10):
+        dt, fmt, layout, side = pick(rng, ["f32", "f64"]), pick(rng, "ORC"), pick(rng, "CR"), pick(rng, "LR")
+        npdt = np.float32 if dt == "f32" else np.float64
+        opA, opB = pick(rng, "NNT"), pick(rng, "NNT")         # opA: the sparse operand, opB: the dense one
+        d, n, m = logint(rng, 1, 400), logint(rng, 1, 300), logint(rng, 1, 3000)
+        alpha, beta = pick(rng, SCALARS)
+        off = small_offsets(rng) if fmt == "O" else (0, 0)
+        density = pick(rng, [0.0, 0.01, 0.05, 0.3])
+        what = dict(dt=dt, fmt=fmt, layout=layout, side=side, opA=opA, opB=opB, d=d, n=n, m=m, alpha=alpha, beta=beta, off=off, density=density)
+        try:
+            # left: C (d x n) = op(A) (d x m) op(B) (m x n); right: C (n x d) = op(B) (n x m) op(A) (m x d)
+            rowsA, colsA = ((d, m) if opA == "N" else (m, d)) if side == "L" else ((m, d) if opA == "N" else (d, m))
+            rowsB, colsB = ((m, n) if opB == "N" else (n, m)) if side == "L" else ((n, m) if opB == "N" else (m, n))
+            rowsC, colsC = (d, n) if side == "L" else (n, d)
+            Afull = random_sparse(rng, rowsA + off[0] + 2, colsA + off[1] + 1, density, npdt) if fmt == "O" else random_sparse(rng, rowsA, colsA, density, npdt)
+            A = to_fmt(rb, cuda, Afull, fmt)
+            ldb = (rowsB if layout == "C" else colsB) + pick(rng, [0, 0, 1, 3])
+            ldc = (rowsC if layout == "C" else colsC) + pick(rng, [0, 0, 2])
+            Bflat = rng.standard_normal(span(layout, rowsB, colsB, ldb)).astype(npdt)
+            C0 = rng.standard_normal(span(layout, rowsC, colsC, ldc)).astype(npdt)
+            dB, dC = torch.from_numpy(Bflat).to(cuda), torch.from_numpy(C0.copy()).to(cuda)
+            L, O = rb.Layout(layout), rb.Op
+            if side == "L":
+                rb.left_spmm(L, O(opA), O(opB), d, n, m, alpha, A, off[0], off[1], dB, ldb, beta, dC, ldc)
+            else:
+                rb.right_spmm(L, O(opB), O(opA), n, d, m, alpha, dB, ldb, A, off[0], off[1], beta, dC, ldc)
+            Ax = Afull[off[0]:off[0] + rowsA, off[1]:off[1] + colsA].astype(np.float64)
+            Aop = Ax if opA == "N" else Ax.T
+            Bop = mat(layout, rowsB, colsB, ldb, Bflat).astype(np.float64)
+            Bop = Bop if opB == "N" else Bop.T
+            got_flat = dC.cpu().numpy()
+            got = mat(layout, rowsC, colsC, ldc, got_flat).astype(np.float64)
+            C0m = mat(layout, rowsC, colsC, ldc, C0).astype(np.float64)
+            # the componentwise bound with the sparse operand in the operator's place
+            check_bound(dt, got, C0m, Aop, Bop, alpha, beta, side, "spmm")
+            mask = np.ones(len(C0), bool)
+            mask[mat(layout, rowsC, colsC, ldc, np.arange(len(C0))).ravel()] = False
+            assert np.array_equal(got_flat[mask], C0[mask]), "padding of C was written"
+        except Exception as e:
+            raise AssertionError(f"spmm draw {block}.{it}: {what}: {e}") from e
+
+
+@pytest.mark.parametrize("block", range(2 * MORE))
+def test_fuzz_sketch_symmetric(rb, cuda, block):
+    """sketch_symmetric (sksy.hh) with random sizes, layouts, sides, families, major axes, operator windows and scalars"""
+    from test_gpu_sketch import mat, span
+    rng = np.random.default_rng(9000 + block)
+    for it in range(10):
+        dt, layout, side = pick(rng, ["f32", "f64"]), pick(rng, "CR"), pick(rng, "LR")
+        npdt = np.float32 if dt == "f32" else np.float64
+        n, d = logint(rng, 1, 700), logint(rng, 1, 200)
+        fam, ma, key = pick(rng, "GU"), pick(rng, "LS"), int(rng.integers(0, 2 ** 31))
+        alpha, beta = pick(rng, SCALARS)
+        off, extra = small_offsets(rng), small_offsets(rng)
+        what = dict(dt=dt, layout=layout, side=side, n=n, d=d, fam=fam, ma=ma, key=key, alpha=alpha, beta=beta, off=off, extra=extra)
+        try:
+            M = rng.standard_normal((n, n)); M = ((M + M.T) / 2).astype(npdt)
+            lda = n + pick(rng, [0, 0, 1, 2])
+            A = np.zeros(span(layout, n, n, lda), npdt)
+            mat(layout, n, n, lda, A)[:] = M
+            dA = torch.from_numpy(A).to(cuda)
+            rowsS, colsS = (d, n) if side == "L" else (n, d)
+            rowsB, colsB = (d, n) if side == "L" else (n, d)
+            Dr, Dc = rowsS + off[0] + extra[0], colsS + off[1] + extra[1]
+            S = rb.DenseSkOp(rb.DenseDist(Dr, Dc, fam, ma), key, dtype=TDT[dt])
+            ldb = (rowsB if layout == "C" else colsB) + pick(rng, [0, 0, 3])
+            B0 = rng.standard_normal(span(layout, rowsB, colsB, ldb)).astype(npdt)
+            dB = torch.from_numpy(B0.copy()).to(cuda)
+            if side == "L":
+                rb.sketch_symmetric(rb.Layout(layout), d, n, alpha, S, off[0], off[1], dA, lda, beta, dB, ldb)
+            else:
+                rb.sketch_symmetric(rb.Layout(layout), n, d, alpha, dA, lda, S, off[0], off[1], beta, dB, ldb)
+            Sx = dense_S(dt, Dr, Dc, fam, ma, [0, 0, 0, 0], [key, 0], rowsS, colsS, off[0], off[1])
+            got = mat(layout, rowsB, colsB, ldb, dB.cpu().numpy()).astype(np.float64)
+            check_bound(dt, got, mat(layout, rowsB, colsB, ldb, B0).astype(np.float64), Sx, M.astype(np.float64), alpha, beta, side, "symmetric")
+        except Exception as e:
+            raise AssertionError(f"symmetric draw {block}.{it}: {what}: {e}") from e
