@@ -189,6 +189,23 @@ def test_sketch_general_dense_tensor_core_path(rb, cuda, monkeypatch):
         assert ratio < 0.05
 
 
+def test_sketch_general_dense_copy_route_by_column_blocks(rb, cuda, monkeypatch):
+    """row-contiguous data with many columns: the k-major copy goes by column blocks that hold the whole contraction axis, each
+    block of C written once. RBX_TC_COPY_MB = 4 makes the blocks 2048 columns wide at m = 512: 5000 columns = two full blocks on
+    the tcgen05 kernel and a last one of 904 columns that falls below the work threshold (SIMT kernel on the copied block)."""
+    monkeypatch.setenv("RBX_TC_COPY_MB", "4")
+    for (side, layout, opA, fam, alpha, beta, ldb_pad) in [("L", "R", "N", "U", 1.5, -0.5, 0), ("L", "R", "N", "G", 1.0, 0.0, 4), ("L", "C", "T", "U", 1.0, 2.0, 0),
+                                                          ("R", "C", "N", "G", 1.0, 0.5, 0)]:
+        l0 = rb.lib.rbx_launch_count()
+        if side == "L":
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, "N", opA, 128, 5000, 512, alpha, beta, off=(2, 4), D_extra=(1, 8), fam=fam, ldb_pad=ldb_pad)
+        else:
+            ratio = run_dense_case(rb, cuda, "f32", side, layout, "N", opA, 128, 512, 5000, alpha, beta, off=(4, 2), D_extra=(8, 1), fam=fam)
+        assert ratio < 0.05
+        assert rb.lib.rbx_launch_count() - l0 >= 7, (side, layout, fam, rb.lib.rbx_launch_count() - l0)
+    monkeypatch.delenv("RBX_TC_COPY_MB")
+
+
 def test_sketch_general_dense_dmma_path(rb, cuda, monkeypatch):
     """double problems inside the DMMA kernel's envelope (rbx_sketch_dense_dmma.cu): ragged M / N / K (odd K included),
     operator offsets, alpha / beta, both families and major axes, both data layouts, the right-sketch form, a pre-filled
