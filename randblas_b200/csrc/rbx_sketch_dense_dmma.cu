@@ -15,10 +15,14 @@
 //   loads of a half-warp hit 16 distinct bank pairs.
 #include "rbx_kernels.cuh"
 #include "rbx_copy.cuh"
+#include "rbx_tma.cuh"
 #include <cstdlib>
 
 #ifndef RBX_DMMA_MIN_N
 #define RBX_DMMA_MIN_N 2         // tall-skinny data: with split-K the padded 128-column tile beats the SIMT kernel
+#endif
+#ifndef RBX_DMMA_MBAR
+#define RBX_DMMA_MBAR 1          // 0: the former pipeline (cp.async groups + one __syncthreads per k-tile)
 #endif
 #ifndef RBX_DMMA_MIN_K
 #define RBX_DMMA_MIN_K 16        // a short contraction axis (lifts): one k-tile is enough to beat the SIMT kernel
@@ -153,6 +157,27 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
 #pragma unroll
         for (int h = 0; h < 4; ++h) { acc[f][h][0] = 0.0; acc[f][h][1] = 0.0; }
 
+#if RBX_DMMA_MBAR
+    // The ring is handed over with two mbarriers per stage instead of one CTA-wide barrier per k-tile: `full` completes when
+    // the cp.async copies of all 256 threads have landed, `empty` when all 8 warps have read the stage. A warp refills the
+    // stage of tile kt - 1 AFTER computing tile kt, so it waits for the other warps only if they are a whole tile behind, and
+    // the two warps of a scheduler drift apart instead of stalling at the same instruction (the barrier version left the
+    // FP64 tensor pipe idle 17 % of the time: barrier + the LDS latency right after it, ncu).
+    __shared__ __align__(8) uint64_t full_bar[DM_STAGES], empty_bar[DM_STAGES];
+    if (tid == 0) {
+        for (int s = 0; s < DM_STAGES; ++s) { mbar_init(&full_bar[s], DM_THREADS); mbar_init(&empty_bar[s], DM_THREADS / 32); }
+        fence_mbar_init();
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < DM_STAGES - 1; ++s)
+        if (s < nk) {
+            load_stage(s, s);
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(smem_u32(&full_bar[s])) : "memory");
+        }
+    for (int kt = 0; kt < nk; ++kt) {
+        mbar_wait(&full_bar[kt % DM_STAGES], (uint32_t)(kt / DM_STAGES) & 1u);
+#else
 #pragma unroll
     for (int s = 0; s < DM_STAGES - 1; ++s) {
         if (s < nk) load_stage(s, s);
@@ -163,6 +188,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         __syncthreads();
         if (kt + DM_STAGES - 1 < nk) load_stage(kt + DM_STAGES - 1, (kt + DM_STAGES - 1) % DM_STAGES);
         cp_async_commit();
+#endif
         const double* Ss = dm_smem + (size_t)(kt % DM_STAGES) * 2 * DM_TILE_DOUBLES;
         const double* Xs = Ss + DM_TILE_DOUBLES;
         const double* pa = Ss + (wm * (8 * MF) + g) * DM_PITCH_K + t;
@@ -179,6 +205,17 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
 #pragma unroll
                 for (int h = 0; h < 4; ++h) dmma884(acc[f][h][0], acc[f][h][1], fa[f], fb[h]);
         }
+#if RBX_DMMA_MBAR
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[kt % DM_STAGES]);
+        const int nxt = kt + DM_STAGES - 1;
+        if (nxt < nk) {
+            const int ls = nxt % DM_STAGES;
+            if (nxt >= DM_STAGES) mbar_wait(&empty_bar[ls], (uint32_t)(nxt / DM_STAGES - 1) & 1u);
+            load_stage(nxt, ls);
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(smem_u32(&full_bar[ls])) : "memory");
+        }
+#endif
     }
     cp_async_wait<0>();
 
