@@ -9,8 +9,8 @@
 // beta = 1. Nothing proportional to d * m is allocated; generation is ~1 % of the FP64 work.
 //
 // dmma_gemm_kernel: C (M x N) = alpha * Sp (M x Kp, k contiguous) * X (Kp x N) + beta * C.
-//   CTA tile 128 x 128 x 16, 8 warps as 2 (M) x 4 (N), warp tile 64 x 32 = 8 x 4 DMMA.8x8x4 fragments (64 accumulators
-//   per thread). Operands come through a 4-stage cp.async ring (16-byte chunks, zero-fill for ragged edges; 8-byte chunks
+//   CTA tile 128 x 128 x 32, 8 warps as 2 (M) x 4 (N), warp tile 64 x 32 = 8 x 4 DMMA.8x8x4 fragments (64 accumulators
+//   per thread). Operands come through a 3-stage cp.async ring (16-byte chunks, zero-fill for ragged edges; 8-byte chunks
 //   for an operand whose base or leading dimension is not 16-byte aligned); rows are padded so that the 8-byte fragment
 //   loads of a half-warp hit 16 distinct bank pairs.
 #include "rbx_kernels.cuh"
@@ -29,11 +29,20 @@
 #endif
 namespace rbx {
 
-constexpr int DM_BM = 128, DM_BN = 128, DM_BK = 16, DM_STAGES = 4, DM_THREADS = 256;
-constexpr int DM_PITCH_K = DM_BK + 4;        // k-contiguous tile: 128 rows x 20 doubles (row shift 32 B mod 128 B)
+#ifndef RBX_DMMA_BK
+#define RBX_DMMA_BK 32          // measured at the C5 slab: 16 x 4 stages 33.2, 16 x 5 33.4, 32 x 3 33.6, 32 x 2 28.7 TFLOP/s
+#endif
+#ifndef RBX_DMMA_STAGES
+#define RBX_DMMA_STAGES 3
+#endif
+constexpr int DM_BM = 128, DM_BN = 128, DM_BK = RBX_DMMA_BK, DM_STAGES = RBX_DMMA_STAGES, DM_THREADS = 256;
+constexpr int DM_CH = DM_BK / 2;             // 16-byte chunks per k-contiguous tile row
+constexpr int DM_PITCH_K = DM_BK + 4;        // k-contiguous tile: 128 rows x (BK + 4) doubles (row shift 32 B mod 128 B)
 constexpr int DM_PITCH_J = DM_BN + 4;        // j-contiguous data tile: 16 rows x 132 doubles
-constexpr int DM_TILE_DOUBLES = DM_BM * DM_PITCH_K;                 // 2560 doubles = 20480 B (>= 16 * 132)
-constexpr size_t DM_SMEM = (size_t) DM_STAGES * 2 * DM_TILE_DOUBLES * sizeof(double);   // 163840 B
+constexpr int DM_TILE_DOUBLES = DM_BM * DM_PITCH_K;                 // 2560 doubles = 20480 B at BK = 16 (>= BK * 132)
+static_assert(DM_BM * DM_PITCH_K >= DM_BK * DM_PITCH_J, "the j-contiguous data tile must fit the operand slot");
+constexpr size_t DM_SMEM = (size_t) DM_STAGES * 2 * DM_TILE_DOUBLES * sizeof(double);   // 163840 B at BK = 16, 4 stages
+static_assert(DM_SMEM >= (size_t) 128 * 136 * sizeof(double) && DM_SMEM <= 227 * 1024, "ring too small for the epilogue staging or too large for an SM");
 
 struct DmmaArgs {
     const double* S; int64_t s_pitch;        // operator panel, S[i * s_pitch + l]
@@ -96,9 +105,9 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         const uint32_t sX = sS + (uint32_t) DM_TILE_DOUBLES * 8u;
         if (a.s16) {
 #pragma unroll
-            for (int q = 0; q < (BM * 8 + DM_THREADS - 1) / DM_THREADS; ++q) {
-                const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
-                if (BM * 8 % DM_THREADS != 0 && row >= BM) break;
+            for (int q = 0; q < (BM * DM_CH + DM_THREADS - 1) / DM_THREADS; ++q) {
+                const int c = tid + q * DM_THREADS, row = c / DM_CH, kc = (c % DM_CH) * 2;
+                if (BM * DM_CH % DM_THREADS != 0 && row >= BM) break;
                 const int64_t gi = i0 + row;
                 const bool ok = gi < a.M;
                 const double* src = Sb + (ok ? gi : 0) * a.s_pitch + (k0 + kc < Kc ? k0 + kc : 0);
@@ -106,8 +115,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
             }
         } else {
 #pragma unroll
-            for (int q = 0; q < BM * 16 / DM_THREADS; ++q) {
-                const int c = tid + q * DM_THREADS, row = c >> 4, kc = c & 15;
+            for (int q = 0; q < BM * DM_BK / DM_THREADS; ++q) {
+                const int c = tid + q * DM_THREADS, row = c / DM_BK, kc = c % DM_BK;
                 const bool ok = i0 + row < a.M && k0 + kc < Kc;
                 cp_async8(sS + (uint32_t)(row * DM_PITCH_K + kc) * 8u, ok ? Sb + (i0 + row) * a.s_pitch + k0 + kc : Sb, ok ? 8 : 0);
             }
@@ -115,8 +124,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         if (!XJ) {
             if (a.x16) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int c = tid + q * DM_THREADS, row = c >> 3, kc = (c & 7) * 2;
+                for (int q = 0; q < DM_BN * DM_CH / DM_THREADS; ++q) {
+                    const int c = tid + q * DM_THREADS, row = c / DM_CH, kc = (c % DM_CH) * 2;
                     const int64_t gj = j0 + row;
                     const bool ok = gj < a.N;
                     const double* src = Xb + (ok ? gj : 0) * a.sx_j + (k0 + kc < Kc ? k0 + kc : 0);
@@ -124,8 +133,8 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
                 }
             } else {
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const int c = tid + q * DM_THREADS, row = c >> 4, kc = c & 15;
+                for (int q = 0; q < DM_BN * DM_BK / DM_THREADS; ++q) {
+                    const int c = tid + q * DM_THREADS, row = c / DM_BK, kc = c % DM_BK;
                     const bool ok = j0 + row < a.N && k0 + kc < Kc;
                     cp_async8(sX + (uint32_t)(row * DM_PITCH_K + kc) * 8u, ok ? Xb + (j0 + row) * a.sx_j + k0 + kc : Xb, ok ? 8 : 0);
                 }
@@ -133,7 +142,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
         } else {
             if (a.x16) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
+                for (int q = 0; q < DM_BK * 64 / DM_THREADS; ++q) {
                     const int c = tid + q * DM_THREADS, l = c >> 6, jc = (c & 63) * 2;
                     const int64_t gl = k0 + l;
                     const bool ok = gl < Kc;
@@ -142,7 +151,7 @@ __global__ void __launch_bounds__(DM_THREADS, 1) dmma_gemm_kernel(const DmmaArgs
                 }
             } else {
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
+                for (int q = 0; q < DM_BK * 128 / DM_THREADS; ++q) {
                     const int c = tid + q * DM_THREADS, l = c >> 7, jc = c & 127;
                     const bool ok = k0 + l < Kc && j0 + jc < a.N;
                     cp_async8(sX + (uint32_t)(l * DM_PITCH_J + jc) * 8u, ok ? Xb + (k0 + l) * a.sx_l + j0 + jc : Xb, ok ? 8 : 0);
@@ -327,7 +336,7 @@ static int launch_dmma_gemm(const DmmaArgs& a_in, int mf, cudaStream_t stream) {
     // few output tiles (tall-skinny data: M x N small, K long): split the contraction axis so that about two waves of CTAs run
     int64_t ksplit = (2 * kNumSMs) / tiles;
     const int64_t nk = (a.K + DM_BK - 1) / DM_BK;
-    if (ksplit > nk / 16) ksplit = nk / 16;                   // at least 16 k-tiles (256 contraction indices) per split
+    if (ksplit > nk / (256 / DM_BK)) ksplit = nk / (256 / DM_BK);   // at least 256 contraction indices per split
     if (ksplit < 1) ksplit = 1;
     if (const char* ev = getenv("RBX_DMMA_KSPLIT")) { const int64_t v = atoll(ev); if (v >= 1 && v <= nk) ksplit = v; }
     a.ntiles = tiles; a.ksplit = (int) ksplit; a.partial = nullptr;
