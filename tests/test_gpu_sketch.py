@@ -829,16 +829,22 @@ def test_host_pointer_padded_B_is_untouched_outside_the_view(rb, cuda, dt):
 
 
 @pytest.mark.parametrize("fmt", ["O", "R", "C"])
-def test_host_pointer_sketch_sparse(rb, cuda, fmt):
+@pytest.mark.parametrize("back", ["whole", "blocks"])
+def test_host_pointer_sketch_sparse(rb, cuda, fmt, back, monkeypatch):
     """rbx_host_sketch_sparsedata_*: the sparse matrix and B in host memory give the device call's bits; B as a window of a
     larger host array (ldb beyond the natural dimension) keeps its padding, with beta == 0 (NaNs in B must not propagate)
-    and with beta != 0; argument errors are reported without touching B"""
+    and with beta != 0; argument errors are reported without touching B. back = "blocks": the result returns in eight column
+    blocks on the auxiliary stream while later blocks are gathered (what results of 256 MB and more do; RBX_SPD_BACK_MB = 0
+    forces it here), contiguous and strided (padded) views."""
+    if back == "blocks":
+        monkeypatch.setenv("RBX_SPD_BACK_MB", "0")
     rng = np.random.default_rng(91)
     for dt in ("f32", "f64"):
         npdt = np.float32 if dt == "f32" else np.float64
         bits = np.uint32 if dt == "f32" else np.uint64
         for (side, layout, d, n, m, pad, beta) in [("L", "C", 24, 300, 500, 0, 0.0), ("L", "C", 24, 40, 500, 7, 0.0), ("L", "R", 12, 130, 260, 5, -0.5),
-                                                  ("R", "C", 16, 200, 90, 3, 0.0), ("R", "R", 16, 200, 90, 0, 1.5)]:
+                                                  ("R", "C", 16, 200, 90, 3, 0.0), ("R", "R", 16, 200, 90, 0, 1.5), ("L", "C", 72, 64, 300, 5, 0.0),
+                                                  ("R", "R", 80, 37, 120, 9, -1.0), ("L", "C", 8, 5, 60, 0, 0.0)]:
             # left: B (d x n) = S (d x m) A (m x n);  right: B (m' x d) = A (m' x n') S (n' x d) with m' = n, n' = m here
             rowsA, colsA = (m, n) if side == "L" else (n, m)
             rowsB, colsB = (d, n) if side == "L" else (n, d)
