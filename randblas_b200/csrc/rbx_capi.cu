@@ -744,6 +744,7 @@ static int host_sketch_sparsedata(char side, char layout, char opS, char opA, in
     struct Back { T* host; const T* dev; HostView v; cudaStream_t copy; cudaEvent_t ev[16]; int nev; bool fail; } back{ B_host, B_dev, vb, nullptr, {}, 0, false };
     ColBlockHook hook{ 1, false, &back, [](void* c, int64_t j0, int64_t j1, cudaStream_t s2) -> int {
         Back& k = *static_cast<Back*>(c);
+        if (j1 <= j0) return RBX_OK;
         cudaEvent_t e = nullptr;
         if (k.nev >= 16 || cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); k.fail = true; return RBX_ERR_CUDA; }
         k.ev[k.nev++] = e;
@@ -761,7 +762,7 @@ static int host_sketch_sparsedata(char side, char layout, char opS, char opA, in
     } };
     size_t back_min = (size_t) 256 << 20;
     if (const char* ev = getenv("RBX_SPD_BACK_MB")) back_min = (size_t) atoll(ev) << 20;      // tests: block-wise copy-back at small sizes
-    if (rc == RBX_OK && vb.span * sizeof(T) >= back_min && p1 >= 8 && !getenv("RBX_NO_SLABS") && (back.copy = aux_stream()) != nullptr) hook.nblocks = 8;
+    if (rc == RBX_OK && vb.span * sizeof(T) >= back_min && ((side == 'L') ? p1 : p0) >= 8 && !getenv("RBX_NO_SLABS") && (back.copy = aux_stream()) != nullptr) hook.nblocks = 8;
     if (rc == RBX_OK) rc = sketch_sparsedata<T>(side, layout, opS, opA, p0, p1, p2, alpha, D_rows, D_cols, family, major_axis, ctr, key, ro_s, co_s,
                                                 fmt, A_rows, A_cols, nnz, vals, i0, i1, ro_a, co_a, beta, B_dev, ldb, (void*) st, &hook);
     if (hook.used) {                                     // the caller's stream outlives the copies (B_dev is freed on it)
