@@ -659,7 +659,7 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
     constexpr int W = SASO_ROWB / (int) sizeof(T);
     constexpr int HALVES = 32 / W;
     constexpr int NS = SASO_RW / HALVES;
-    constexpr size_t SMEM_MAX = 227 * 1024;
+    constexpr size_t SMEM_MAX = 227 * 1024 - 512;     // dynamic shared memory: the opt-in limit of a CTA less the kernels' static part (the tile kernel's mbarriers)
     // envelope of this kernel; everything else goes to the general path
     const bool cols_contig = (sx_l == 1 && (sx_j != 1 || N == 1));      // a single column is column-contiguous whatever its leading dimension says
     if (!cols_contig && sx_j != 1) return RBX_ERR_UNSUPPORTED;
@@ -759,6 +759,8 @@ int launch_saso_fast(const Ctr128& ctr, const Key64& key, int64_t S_rows, int64_
         tile_spill<<<grid, SASO_TILE_THREADS, smem, stream>>>(a);      // returns at once unless the prep kernel raised the flag
         count_launch(); count_launch();
         rc = check_launch("saso_tile_kernel");
+        if (rc != RBX_OK) std::fprintf(stderr, "[rbx] saso_tile_kernel launch: grid %u, threads %d, dynamic smem %zu, CK %d, cap %d, M %lld, N %lld, K %lld, vec_nnz %lld, R %d, msplit %d\n",
+                                       grid, (int) SASO_TILE_THREADS, smem, CK, cap, (long long) M, (long long) N, (long long) K, (long long) vec_nnz, R, msplit);
         if (rc == RBX_OK && !direct) {
             int64_t blocks = (M * N + 255) / 256;
             if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;

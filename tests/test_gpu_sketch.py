@@ -408,6 +408,12 @@ def test_saso_small_windows_are_replicated(rb, cuda, dt, monkeypatch):
     assert torch.allclose(outs[0], outs[2], rtol=tol, atol=tol * float(outs[2].abs().max()))
 
 
+def test_saso_ring_fills_shared_memory_to_the_byte(rb, cuda):
+    """a draw of the randomized tests (block 186 of a 40x sweep): 15 x 554 window, vec_nnz = 24, 7 columns -- the ring stages came to
+    exactly 227 KB of dynamic shared memory, which with the kernel's static mbarriers was one launch-time 'invalid argument'"""
+    run_sparseop_case(rb, cuda, "f32", "R", "R", "T", "T", 15, 554, 7, -0.7, 1.0, 24, "S", D_extra=(7, 6), off=(2, 4), key=1523932692, lda_pad=1)
+
+
 @pytest.mark.parametrize("dt", ["f32", "f64"])
 def test_saso_tail_paths(rb, cuda, dt, monkeypatch):
     """The streaming SASO kernel's three homes of an entry: the slot record (first three per row and chunk), the staged
