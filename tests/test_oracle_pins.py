@@ -105,6 +105,40 @@ def test_oracle_vs_compiled_reference_random():
         assert a[4] == b[4]
 
 
+@pytest.mark.skipif(ol.REF is None, reason="compiled reference (oracle/_ref) not built on this machine")
+def test_oracle_vs_compiled_reference_random_larger():
+    """the same comparison at the sizes the randomized GPU tests draw from (tests/test_gpu_fuzz.py checks the device against the
+    oracle): long Fisher-Yates vectors (vec_nnz up to 700, full permutations included), both major axes, wide and tall; dense
+    windows of operators with thousands of rows / columns and counters about to carry"""
+    rng = np.random.default_rng(17)
+    for _ in range(24):
+        r, c = int(rng.integers(1, 3000)), int(rng.integers(1, 3000))
+        ma = "SL"[rng.integers(2)]
+        k = int(min(r, c, [1, 8, 17, 33, 129, 700][rng.integers(6)]))
+        if rng.random() < 0.2:
+            k = min(r, c)                       # a full permutation of the short axis
+        while k * (max(r, c) if ma == "S" else min(r, c)) > 1500000:
+            k = max(1, k // 2)
+        key, ctr = [int(rng.integers(0, 2**32)), int(rng.integers(0, 2**32))], [0xFFFFFF00, 0xFFFFFFFF, int(rng.integers(0, 2**32)), 0]
+        it = ("i32", "i64")[rng.integers(2)]
+        a = ol.fill_sparse("f32", it, r, c, k, ma, ctr, key, "orc")
+        b = ol.fill_sparse("f32", it, r, c, k, ma, ctr, key, "ref")
+        assert a[0] == b[0] == 0
+        for x, y in zip(a[1:4], b[1:4]):
+            assert np.array_equal(x, y), (r, c, k, ma)
+        assert a[4] == b[4]
+    for _ in range(24):
+        R, C = int(rng.integers(1, 3000)), int(rng.integers(1, 3000))
+        nr, nc = int(rng.integers(1, min(R, 300) + 1)), int(rng.integers(1, min(C, 300) + 1))
+        ro, co = int(rng.integers(0, R - nr + 1)), int(rng.integers(0, C - nc + 1))
+        fam, ma, lay, dt = "GU"[rng.integers(2)], "LS"[rng.integers(2)], "CR"[rng.integers(2)], ("f32", "f64")[rng.integers(2)]
+        ctr = [0xFFFFFFFF - int(rng.integers(0, 100000)), 0xFFFFFFFF, int(rng.integers(0, 2**32)), 0]
+        key = [int(rng.integers(0, 2**32)), int(rng.integers(0, 2**32))]
+        a = ol.fill_dense(dt, lay, R, C, fam, ma, nr, nc, ro, co, ctr, key, "orc")
+        b = ol.fill_dense(dt, lay, R, C, fam, ma, nr, nc, ro, co, ctr, key, "ref")
+        assert a[0] == b[0] == 0 and np.array_equal(bits(a[1]), bits(b[1])) and a[2] == b[2], (R, C, nr, nc, ro, co, fam, ma, lay, dt)
+
+
 def test_uniform_transforms_documented_properties():
     """Random123's u01 / uneg11 (uniform.hpp) are restated in oracle/shims (no checkout offline). Their documented contract
     pins the restatement at the edges: u01<float> maps into (0, 1] -- never 0, exactly 1 at the top word -- and is
